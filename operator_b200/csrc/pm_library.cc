@@ -1,0 +1,429 @@
+// Pattern-library compiler.  See pm_library.h.
+#include "pm_library.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+
+#include "pm_json.h"
+
+namespace pm {
+
+namespace {
+
+constexpr int kUnitMaxStates = 4096;       // verify DFA of one regex
+constexpr int kUnitNfaBudget = 20000;
+constexpr int kGroupTableBytes = 96 * 1024;   // combined DFA must fit shared memory next to the text tile
+constexpr int kGroupMaxStates = 8192;
+constexpr int kGroupNfaBudget = 400000;
+
+const char *kStackRegex = "^(?:\\s+at\\s|Caused by:|\\s+\\.\\.\\.\\s\\d+\\s(?:more|common frames omitted)|\\s+Suppressed:)";
+const char *kSeverities[5] = {"INFO", "LOW", "MEDIUM", "HIGH", "CRITICAL"};
+const double kSevMult[5] = {0.2, 0.4, 0.6, 0.8, 1.0};
+
+struct CompileFail {
+    int status, pattern, secondary, offset;
+    std::string id, msg;
+};
+
+struct Section {
+    std::vector<uint8_t> bytes;
+    template <class T>
+    size_t push(const T &v) {
+        size_t at = bytes.size();
+        bytes.resize(at + sizeof(T));
+        memcpy(bytes.data() + at, &v, sizeof(T));
+        return at;
+    }
+    size_t push_raw(const void *p, size_t n) {
+        size_t at = bytes.size();
+        bytes.resize(at + n);
+        if (n) memcpy(bytes.data() + at, p, n);
+        return at;
+    }
+};
+
+std::string str_of(const JsonValue *v, const char *dflt = "") {
+    if (!v) return dflt;
+    if (v->type == JsonValue::String) return v->str;
+    if (v->type == JsonValue::Number) return json_number(v->num);
+    return dflt;
+}
+
+bool num_of(const JsonValue *v, double &out) {
+    if (!v || v->type != JsonValue::Number) return false;
+    out = v->num;
+    return true;
+}
+
+// Cost of sampling the 7-byte window at `o`: expected filter hits per text word (lower is
+// better); windows that touch a case-insensitive position are pushed back because they force
+// the whole library into fold mode.
+double window_cost(const Literal &l, size_t o) {
+    double cost = 0;
+    for (int k = 0; k < 4; k++) {
+        int bits = 0;
+        for (int j = 0; j < kGramLen; j++) bits += byte_rarity(l.bytes[o + k + j]);
+        cost += std::ldexp(1.0, -bits);
+    }
+    for (size_t j = o; j < o + kMinLiteral; j++)
+        if (l.mask[j]) cost += 1.0;
+    return cost;
+}
+
+uint32_t gram_at(const Literal &l, size_t o, bool fold) {
+    uint32_t g = 0;
+    for (int j = 0; j < kGramLen; j++) g |= (uint32_t)l.bytes[o + j] << (8 * j);
+    return fold ? (g | 0x20202020u) : g;
+}
+
+struct Unit {
+    Dfa dfa;
+};
+
+void compile_unit(const std::string &rx, int pattern, int secondary, const std::string &id, Dfa &dfa, NodePtr *ast_out) {
+    RegexError err;
+    NodePtr ast = parse_regex(rx, err);
+    if (!ast) throw CompileFail{err.status, pattern, secondary, err.offset, id, err.message};
+    Nfa nfa;
+    if (!nfa.add(*ast, 0, kUnitNfaBudget))
+        throw CompileFail{PM_E_TOO_COMPLEX, pattern, secondary, -1, id, "regex expands to too many NFA states"};
+    if (!build_search_dfa(nfa, /*early_accept=*/true, kUnitMaxStates, dfa))
+        throw CompileFail{PM_E_TOO_COMPLEX, pattern, secondary, -1, id, "DFA state limit exceeded"};
+    if (ast_out) *ast_out = std::move(ast);
+}
+
+struct GroupBuild {
+    Dfa dfa;
+    std::vector<int> patterns;
+};
+
+// Packs tier-2 primaries into as few combined DFAs as fit the shared-memory budget.
+void build_groups(const std::vector<int> &pats, const std::vector<NodePtr> &asts, const std::vector<PatternInfo> &info,
+                  std::vector<GroupBuild> &out) {
+    if (pats.empty()) return;
+    Nfa nfa;
+    bool ok = true;
+    for (size_t u = 0; u < pats.size() && ok; u++) ok = nfa.add(*asts[pats[u]], (int)u, kGroupNfaBudget);
+    GroupBuild g;
+    if (ok) ok = build_search_dfa(nfa, /*early_accept=*/false, kGroupMaxStates, g.dfa);
+    if (ok) ok = (size_t)g.dfa.nstates * g.dfa.stride() * 2 <= (size_t)kGroupTableBytes;
+    if (ok) {
+        g.patterns = pats;
+        out.push_back(std::move(g));
+        return;
+    }
+    if (pats.size() == 1)
+        throw CompileFail{PM_E_TOO_COMPLEX, pats[0], -1, -1, info[pats[0]].id,
+                          "regex has no literal of 7+ bytes and its scan DFA exceeds the shared-memory budget"};
+    std::vector<int> a(pats.begin(), pats.begin() + pats.size() / 2), b(pats.begin() + pats.size() / 2, pats.end());
+    build_groups(a, asts, info, out);
+    build_groups(b, asts, info, out);
+}
+
+size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+}  // namespace
+
+int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile_report &rep) {
+    memset(&rep, 0, sizeof rep);
+    rep.pattern_index = rep.secondary_index = rep.regex_offset = -1;
+    out = CompiledLibrary();
+    try {
+        JsonValue root;
+        std::string jerr;
+        size_t joff = 0;
+        if (!json_parse(spec, n, root, jerr, &joff))
+            throw CompileFail{PM_E_SYNTAX, -1, -1, (int)joff, "", "library JSON: " + jerr};
+        std::vector<const JsonValue *> libs;
+        if (root.type == JsonValue::Array)
+            for (auto &v : root.arr) libs.push_back(&v);
+        else
+            libs.push_back(&root);
+
+        std::vector<PatternDesc> pdesc;
+        std::vector<SecDesc> sdesc;
+        std::vector<Dfa> &units = out.unit_dfas;
+        std::vector<NodePtr> asts;
+
+        for (const JsonValue *lib : libs) {
+            if (lib->type != JsonValue::Object) throw CompileFail{PM_E_SYNTAX, -1, -1, -1, "", "library must be a JSON object"};
+            const JsonValue *pats = lib->get("patterns");
+            if (!pats) continue;
+            if (pats->type != JsonValue::Array) throw CompileFail{PM_E_SYNTAX, -1, -1, -1, "", "\"patterns\" must be an array"};
+            for (auto &p : pats->arr) {
+                int idx = (int)out.patterns.size();
+                if (p.type != JsonValue::Object) throw CompileFail{PM_E_SYNTAX, idx, -1, -1, "", "pattern must be an object"};
+                PatternInfo pi;
+                pi.id = str_of(p.get("id"));
+                pi.name = str_of(p.get("name"));
+                pi.category = str_of(p.get("category"));
+                std::string sev = str_of(p.get("severity"), "INFO");
+                for (auto &c : sev) c = (char)toupper((unsigned char)c);
+                int rank = -1;
+                for (int i = 0; i < 5; i++)
+                    if (sev == kSeverities[i]) rank = i;
+                if (rank < 0) throw CompileFail{PM_E_SYNTAX, idx, -1, -1, pi.id, "unknown severity '" + sev + "'"};
+                pi.severity = sev;
+                const JsonValue *prim = p.get("primary_pattern");
+                const JsonValue *rx = prim ? prim->get("regex") : nullptr;
+                if (!rx || rx->type != JsonValue::String)
+                    throw CompileFail{PM_E_SYNTAX, idx, -1, -1, pi.id, "primary_pattern.regex missing"};
+                pi.regex = rx->str;
+
+                PatternDesc d;
+                memset(&d, 0, sizeof d);
+                d.confidence = 1.0;
+                num_of(prim->get("confidence"), d.confidence);
+                d.mult = kSevMult[rank];
+                d.severity = (uint32_t)rank;
+                if (const JsonValue *ctx = p.get("context_extraction")) {
+                    double v;
+                    if (num_of(ctx->get("lines_before"), v)) d.lines_before = (int32_t)v;
+                    if (num_of(ctx->get("lines_after"), v)) d.lines_after = (int32_t)v;
+                    const JsonValue *st = ctx->get("include_stack_trace");
+                    if (st && st->type == JsonValue::Bool) d.include_stack = st->b;
+                }
+                if (d.lines_before < 0 || d.lines_after < 0 || d.lines_before > 100000 || d.lines_after > 100000)
+                    throw CompileFail{PM_E_SYNTAX, idx, -1, -1, pi.id, "context_extraction out of range"};
+
+                // primary regex -> verify DFA (+ AST kept for literal analysis / grouping)
+                d.unit = (uint32_t)units.size();
+                units.emplace_back();
+                NodePtr ast;
+                compile_unit(pi.regex, idx, -1, pi.id, units.back(), &ast);
+                asts.push_back(std::move(ast));
+
+                d.sec_first = (uint32_t)sdesc.size();
+                if (const JsonValue *secs = p.get("secondary_patterns")) {
+                    if (secs->type != JsonValue::Array && secs->type != JsonValue::Null)
+                        throw CompileFail{PM_E_SYNTAX, idx, -1, -1, pi.id, "secondary_patterns must be an array"};
+                    if (secs->arr.size() > (size_t)kMaxSecondary)
+                        throw CompileFail{PM_E_SYNTAX, idx, -1, -1, pi.id, "more than 8 secondary patterns"};
+                    int j = 0;
+                    for (auto &s : secs->arr) {
+                        const JsonValue *srx = s.get("regex");
+                        if (!srx || srx->type != JsonValue::String)
+                            throw CompileFail{PM_E_SYNTAX, idx, j, -1, pi.id, "secondary regex missing"};
+                        SecDesc sd;
+                        memset(&sd, 0, sizeof sd);
+                        double v;
+                        if (num_of(s.get("weight"), v)) sd.weight = v;
+                        if (num_of(s.get("proximity_window"), v)) sd.window = (int32_t)v;
+                        if (sd.window < 0 || sd.window > 10000)
+                            throw CompileFail{PM_E_SYNTAX, idx, j, -1, pi.id, "proximity_window out of range"};
+                        sd.unit = (uint32_t)units.size();
+                        units.emplace_back();
+                        compile_unit(srx->str, idx, j, pi.id, units.back(), nullptr);
+                        sdesc.push_back(sd);
+                        j++;
+                    }
+                }
+                d.sec_count = (uint32_t)sdesc.size() - d.sec_first;
+
+                std::string mj = "{\"id\":";
+                json_escape(pi.id, mj);
+                mj += ",\"name\":";
+                json_escape(pi.name, mj);
+                mj += ",\"severity\":";
+                json_escape(pi.severity, mj);
+                mj += ",\"category\":";
+                json_escape(pi.category, mj);
+                if (const JsonValue *rem = p.get("remediation")) {
+                    mj += ",\"remediation\":";
+                    mj.append(spec + rem->raw_begin, rem->raw_end - rem->raw_begin);
+                }
+                mj += "}";
+                pi.meta_json = std::move(mj);
+                out.patterns.push_back(std::move(pi));
+                pdesc.push_back(d);
+            }
+        }
+        const int P = (int)out.patterns.size();
+        // built-in STACK unit (SPEC.md section 6)
+        uint32_t stack_unit = (uint32_t)units.size();
+        units.emplace_back();
+        compile_unit(kStackRegex, -1, -1, "<stack>", units.back(), nullptr);
+
+        // ---- tiering: literal-gram filter where a 7+ byte literal is required, DFA otherwise
+        out.literals.resize(P);
+        std::vector<int> tier2;
+        for (int i = 0; i < P; i++) {
+            int q = 0;
+            std::vector<Literal> lits = required_literals(*asts[i], &q);
+            if (q >= kMinLiteral) {
+                out.literals[i] = std::move(lits);
+                pdesc[i].tier = 1;
+            } else {
+                pdesc[i].tier = 2;
+                tier2.push_back(i);
+            }
+            out.patterns[i].tier = (int)pdesc[i].tier;
+        }
+
+        // ---- gram selection
+        struct Chosen {
+            int pattern;
+            const Literal *lit;
+            size_t o;
+        };
+        std::vector<Chosen> chosen;
+        bool fold = false;
+        for (int i = 0; i < P; i++)
+            for (auto &l : out.literals[i]) {
+                size_t best_o = 0;
+                double best = 1e300;
+                for (size_t o = 0; o + kMinLiteral <= l.bytes.size(); o++) {
+                    double c = window_cost(l, o);
+                    if (c < best) best = c, best_o = o;
+                }
+                for (size_t j = best_o; j < best_o + kMinLiteral; j++)
+                    if (l.mask[j]) fold = true;
+                chosen.push_back({i, &l, best_o});
+            }
+        Section litpool, probes_sec;
+        std::map<uint32_t, std::vector<Probe>> by_gram;
+        for (auto &c : chosen) {
+            uint32_t lit_off = (uint32_t)litpool.push_raw(c.lit->bytes.data(), c.lit->bytes.size());
+            litpool.push_raw(c.lit->mask.data(), c.lit->mask.size());
+            for (int k = 0; k < 4; k++) {
+                Probe pr;
+                pr.pattern = (uint32_t)c.pattern;
+                pr.lit_off = lit_off;
+                pr.lit_len = (uint16_t)c.lit->bytes.size();
+                pr.gram_off = (uint16_t)(c.o + k);
+                by_gram[gram_at(*c.lit, c.o + k, fold)].push_back(pr);
+            }
+        }
+        const uint32_t n_grams = (uint32_t)by_gram.size();
+        uint32_t log2_bits = 0, log2_cap = 4;
+        if (n_grams) {
+            log2_bits = 15;
+            while (log2_bits < 20 && (1ull << log2_bits) < 512ull * n_grams) log2_bits++;
+            while ((1u << log2_cap) < 2 * n_grams) log2_cap++;
+        }
+        std::vector<uint32_t> bitmap(log2_bits ? (1u << log2_bits) / 32 : 4, 0);
+        std::vector<uint32_t> gkeys(1u << log2_cap, kGramEmpty), gfirst(1u << log2_cap, 0), gcount(1u << log2_cap, 0);
+        uint32_t n_probes = 0;
+        for (auto &kv : by_gram) {
+            uint32_t bit = gram_filter_bit(kv.first, log2_bits);
+            bitmap[bit >> 5] |= 1u << (bit & 31);
+            uint32_t slot = gram_table_slot(kv.first, log2_cap);
+            while (gkeys[slot] != kGramEmpty) slot = (slot + 1) & ((1u << log2_cap) - 1);
+            gkeys[slot] = kv.first;
+            gfirst[slot] = n_probes;
+            gcount[slot] = (uint32_t)kv.second.size();
+            for (auto &pr : kv.second) probes_sec.push(pr), n_probes++;
+        }
+
+        // ---- combined DFAs for tier 2
+        std::vector<GroupBuild> groups;
+        build_groups(tier2, asts, out.patterns, groups);
+
+        // ---- tables
+        Section units_sec, classmaps, tables, groups_sec, gaccept;
+        auto put_dfa = [&](const Dfa &d, uint32_t &table_off, uint32_t &cm_off) {
+            cm_off = (uint32_t)classmaps.push_raw(d.classmap, 256);
+            table_off = (uint32_t)(tables.bytes.size() / 2);
+            tables.push_raw(d.next.data(), d.next.size() * 2);
+        };
+        for (auto &d : units) {
+            UnitDesc u;
+            memset(&u, 0, sizeof u);
+            put_dfa(d, u.table_off, u.classmap_off);
+            u.nstates = (uint16_t)d.nstates;
+            u.stride = (uint16_t)d.stride();
+            u.accept_state = (uint16_t)d.first_accept;   // early-accept: one sticky state
+            if (d.first_accept >= d.nstates)
+                throw CompileFail{PM_E_UNSUPPORTED, -1, -1, -1, "", "regex can never match"};
+            units_sec.push(u);
+        }
+        for (auto &g : groups) {
+            GroupDesc gd;
+            memset(&gd, 0, sizeof gd);
+            put_dfa(g.dfa, gd.table_off, gd.classmap_off);
+            gd.nstates = (uint16_t)g.dfa.nstates;
+            gd.stride = (uint16_t)g.dfa.stride();
+            gd.first_accept = (uint16_t)g.dfa.first_accept;
+            gd.accept_off = (uint32_t)(gaccept.bytes.size() / 4);
+            uint32_t na = (uint32_t)g.dfa.accept.size(), run = na + 1;
+            for (uint32_t a = 0; a < na; a++) {
+                gaccept.push(run);
+                run += (uint32_t)g.dfa.accept[a].size();
+            }
+            gaccept.push(run);
+            for (auto &lst : g.dfa.accept)
+                for (int u : lst) gaccept.push((uint32_t)g.patterns[u]);
+            groups_sec.push(gd);
+            out.group_dfas.push_back(g.dfa);
+            out.group_patterns.push_back(g.patterns);
+        }
+
+        // ---- assemble
+        BlobHeader h;
+        memset(&h, 0, sizeof h);
+        h.magic = kBlobMagic;
+        h.version = kBlobVersion;
+        h.n_patterns = (uint32_t)P;
+        h.n_units = (uint32_t)units.size();
+        h.n_secondaries = (uint32_t)sdesc.size();
+        h.stack_unit = stack_unit;
+        h.filter_log2_bits = log2_bits;
+        h.filter_fold = fold;
+        h.gram_log2_cap = log2_cap;
+        h.n_grams = n_grams;
+        h.n_probes = n_probes;
+        h.n_groups = (uint32_t)groups.size();
+        std::vector<uint8_t> &blob = out.blob;
+        blob.assign(align16(sizeof h), 0);
+        auto place = [&](const void *p, size_t nbytes) -> uint64_t {
+            size_t at = align16(blob.size());
+            blob.resize(at + nbytes, 0);
+            if (nbytes) memcpy(blob.data() + at, p, nbytes);
+            blob.resize(align16(blob.size()), 0);
+            return at;
+        };
+        h.off_bitmap = place(bitmap.data(), bitmap.size() * 4);
+        h.off_gram_keys = place(gkeys.data(), gkeys.size() * 4);
+        h.off_gram_first = place(gfirst.data(), gfirst.size() * 4);
+        h.off_gram_count = place(gcount.data(), gcount.size() * 4);
+        h.off_probes = place(probes_sec.bytes.data(), probes_sec.bytes.size());
+        h.off_litpool = place(litpool.bytes.data(), litpool.bytes.size());
+        h.off_units = place(units_sec.bytes.data(), units_sec.bytes.size());
+        h.off_classmaps = place(classmaps.bytes.data(), classmaps.bytes.size());
+        h.off_tables = place(tables.bytes.data(), tables.bytes.size());
+        h.off_patterns = place(pdesc.data(), pdesc.size() * sizeof(PatternDesc));
+        h.off_secondaries = place(sdesc.data(), sdesc.size() * sizeof(SecDesc));
+        h.off_groups = place(groups_sec.bytes.data(), groups_sec.bytes.size());
+        h.off_group_accept = place(gaccept.bytes.data(), gaccept.bytes.size());
+        h.total_bytes = blob.size();
+        memcpy(blob.data(), &h, sizeof h);
+
+        rep.status = PM_OK;
+        rep.n_patterns = P;
+        rep.n_regex_units = (int)units.size();
+        rep.n_filtered = P - (int)tier2.size();
+        rep.n_dfa_scanned = (int)tier2.size();
+        rep.n_grams = (int)n_grams;
+        rep.filter_log2_bits = (int)log2_bits;
+        rep.filter_fold_case = fold;
+        rep.dfa_groups = (int)groups.size();
+        for (auto &g : groups) rep.dfa_states += g.dfa.nstates, rep.dfa_classes = std::max(rep.dfa_classes, g.dfa.ncls);
+        rep.blob_bytes = (int64_t)blob.size();
+        snprintf(rep.message, sizeof rep.message, "ok");
+        return PM_OK;
+    } catch (const CompileFail &f) {
+        rep.status = f.status;
+        rep.pattern_index = f.pattern;
+        rep.secondary_index = f.secondary;
+        rep.regex_offset = f.offset;
+        snprintf(rep.pattern_id, sizeof rep.pattern_id, "%s", f.id.c_str());
+        snprintf(rep.message, sizeof rep.message, "%s", f.msg.c_str());
+        out = CompiledLibrary();
+        return f.status;
+    }
+}
+
+}  // namespace pm

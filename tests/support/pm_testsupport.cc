@@ -1,0 +1,158 @@
+// TEST SUPPORT ONLY -- not part of libpodmortem_scan.so and never loaded by the product.
+//
+// Exposes the pattern compiler's intermediate results (verify DFAs, combined DFAs, literals,
+// gram filter) to the CPU test-suite so that compiled tables can be diffed against the oracle
+// without a GPU.  The table walks below are a unit-test harness for host code, not a scan path.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../operator_b200/csrc/pm_library.h"
+
+using namespace pm;
+
+namespace pm {
+bool dfa_line_accepts(const Dfa &d, const uint8_t *line, size_t n, std::vector<int> *units) {
+    uint32_t s = 0;
+    const int stride = d.stride();
+    bool any = false;
+    auto visit = [&](uint32_t st) {
+        if ((int)st >= d.first_accept) {
+            any = true;
+            if (units)
+                for (int u : d.accept[st - d.first_accept]) units->push_back(u);
+        }
+    };
+    for (size_t i = 0; i < n; i++) {
+        s = d.next[(size_t)s * stride + d.classmap[line[i]]];
+        visit(s);
+    }
+    s = d.next[(size_t)s * stride + d.ncls];
+    visit(s);
+    return any;
+}
+}  // namespace pm
+
+extern "C" {
+
+struct pmt_lib {
+    CompiledLibrary lib;
+    std::string scratch;
+};
+
+int pmt_compile(const char *spec, size_t n, pmt_lib **out, pm_compile_report *rep) {
+    pmt_lib *l = new pmt_lib();
+    int rc = compile_library(spec, n, l->lib, *rep);
+    if (rc != PM_OK) {
+        delete l;
+        *out = nullptr;
+        return rc;
+    }
+    *out = l;
+    return PM_OK;
+}
+
+void pmt_free(pmt_lib *l) { delete l; }
+
+int pmt_n_patterns(pmt_lib *l) { return (int)l->lib.patterns.size(); }
+int pmt_pattern_tier(pmt_lib *l, int p) { return l->lib.patterns[p].tier; }
+
+static const PatternDesc *pdesc(pmt_lib *l) {
+    return reinterpret_cast<const PatternDesc *>(l->lib.blob.data() + l->lib.header()->off_patterns);
+}
+static const SecDesc *sdesc(pmt_lib *l) {
+    return reinterpret_cast<const SecDesc *>(l->lib.blob.data() + l->lib.header()->off_secondaries);
+}
+
+int pmt_primary_match(pmt_lib *l, int p, const uint8_t *line, size_t n) {
+    return dfa_line_accepts(l->lib.unit_dfas[pdesc(l)[p].unit], line, n, nullptr);
+}
+int pmt_secondary_match(pmt_lib *l, int p, int j, const uint8_t *line, size_t n) {
+    return dfa_line_accepts(l->lib.unit_dfas[sdesc(l)[pdesc(l)[p].sec_first + j].unit], line, n, nullptr);
+}
+int pmt_stack_match(pmt_lib *l, const uint8_t *line, size_t n) {
+    return dfa_line_accepts(l->lib.unit_dfas[l->lib.header()->stack_unit], line, n, nullptr);
+}
+int pmt_unit_states(pmt_lib *l, int p) { return l->lib.unit_dfas[pdesc(l)[p].unit].nstates; }
+
+// Combined DFAs: which tier-2 patterns does the line match?  Returns the count written.
+int pmt_group_match(pmt_lib *l, const uint8_t *line, size_t n, int *out, int cap) {
+    std::vector<int> pats;
+    for (size_t g = 0; g < l->lib.group_dfas.size(); g++) {
+        std::vector<int> units;
+        dfa_line_accepts(l->lib.group_dfas[g], line, n, &units);
+        for (int u : units) pats.push_back(l->lib.group_patterns[g][u]);
+    }
+    std::sort(pats.begin(), pats.end());
+    pats.erase(std::unique(pats.begin(), pats.end()), pats.end());
+    int k = 0;
+    for (int p : pats)
+        if (k < cap) out[k++] = p;
+    return (int)pats.size();
+}
+
+// Emulates the gram filter + gram table + literal confirmation on a text whose first byte sits
+// at alignment `phase` (0..3) of the device buffer.  Returns 1 if pattern p would be handed to
+// its verify DFA for this text.
+int pmt_filter_triggers(pmt_lib *l, int p, const uint8_t *text, size_t n, int phase) {
+    const BlobHeader *h = l->lib.header();
+    if (!h->filter_log2_bits) return 0;
+    const uint8_t *b = l->lib.blob.data();
+    const uint32_t *bitmap = (const uint32_t *)(b + h->off_bitmap);
+    const uint32_t *gk = (const uint32_t *)(b + h->off_gram_keys);
+    const uint32_t *gf = (const uint32_t *)(b + h->off_gram_first);
+    const uint32_t *gc = (const uint32_t *)(b + h->off_gram_count);
+    const Probe *pr = (const Probe *)(b + h->off_probes);
+    const uint8_t *lp = b + h->off_litpool;
+    size_t first = (4 - (size_t)phase) & 3;
+    for (size_t i = first; i + 4 <= n; i += 4) {
+        uint32_t g;
+        memcpy(&g, text + i, 4);
+        if (h->filter_fold) g |= 0x20202020u;
+        uint32_t bit = gram_filter_bit(g, h->filter_log2_bits);
+        if (!((bitmap[bit >> 5] >> (bit & 31)) & 1)) continue;
+        uint32_t mask = (1u << h->gram_log2_cap) - 1, slot = gram_table_slot(g, h->gram_log2_cap);
+        while (gk[slot] != kGramEmpty && gk[slot] != g) slot = (slot + 1) & mask;
+        if (gk[slot] != g) continue;
+        for (uint32_t k = gf[slot]; k < gf[slot] + gc[slot]; k++) {
+            if ((int)pr[k].pattern != p) continue;
+            if (i < pr[k].gram_off) continue;
+            size_t st = i - pr[k].gram_off;
+            if (st + pr[k].lit_len > n) continue;
+            const uint8_t *lit = lp + pr[k].lit_off, *m = lit + pr[k].lit_len;
+            bool eq = true;
+            for (size_t j = 0; j < pr[k].lit_len && eq; j++) eq = ((text[st + j] | m[j]) == lit[j]);
+            if (eq) return 1;
+        }
+    }
+    return 0;
+}
+
+// JSON list of the required literals of pattern p (bytes shown as latin-1 escaped), for test diagnostics.
+const char *pmt_literals(pmt_lib *l, int p) {
+    std::string &s = l->scratch;
+    s = "[";
+    bool firstl = true;
+    for (auto &lit : l->lib.literals[p]) {
+        if (!firstl) s += ",";
+        firstl = false;
+        s += "\"";
+        for (size_t i = 0; i < lit.bytes.size(); i++) {
+            char buf[8];
+            uint8_t c = lit.bytes[i];
+            if (c >= 0x20 && c < 0x7F && c != '"' && c != '\\')
+                s.push_back((char)c);
+            else {
+                snprintf(buf, sizeof buf, "\\\\x%02x", c);
+                s += buf;
+            }
+        }
+        s += "\"";
+    }
+    s += "]";
+    return s.c_str();
+}
+
+}  // extern "C"
