@@ -6,11 +6,11 @@
 NVCC ?= /usr/local/cuda/bin/nvcc
 CXX ?= g++
 ARCH := -gencode arch=compute_100a,code=sm_100a
-CXXFLAGS := -O2 -std=c++17 -fPIC -Wall -Wno-unused-function -Iinclude
+CXXFLAGS := -O2 -std=c++17 -fPIC -Wall -Wno-unused-function -Iinclude -I/usr/local/cuda/include
 NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Iinclude -Xptxas -v --fmad=false
 
 CSRC := operator_b200/csrc
-HOST_SRCS := $(CSRC)/pm_json.cc $(CSRC)/pm_regex.cc $(CSRC)/pm_automata.cc $(CSRC)/pm_literal.cc $(CSRC)/pm_library.cc
+HOST_SRCS := $(CSRC)/pm_json.cc $(CSRC)/pm_regex.cc $(CSRC)/pm_automata.cc $(CSRC)/pm_literal.cc $(CSRC)/pm_library.cc $(CSRC)/pm_service.cc
 HOST_OBJS := $(HOST_SRCS:.cc=.o)
 CU_SRCS := $(wildcard $(CSRC)/*.cu)
 CU_OBJS := $(CU_SRCS:.cu=.o)
@@ -27,7 +27,7 @@ $(CSRC)/%.o: $(CSRC)/%.cu $(HDRS)
 operator_b200/libpodmortem_scan.so: $(HOST_OBJS) $(CU_OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart
 
-tests/support/libpm_testsupport.so: tests/support/pm_testsupport.cc $(HOST_OBJS)
+tests/support/libpm_testsupport.so: tests/support/pm_testsupport.cc $(filter-out $(CSRC)/pm_service.o,$(HOST_OBJS))
 	$(CXX) $(CXXFLAGS) -shared -o $@ $^
 
 oracle/_build/liboracle_pcre2.so: oracle/scan_pcre2.c

@@ -1,0 +1,757 @@
+// sm_100a kernels of the log-scan path.  Everything here is HBM-bound integer/byte work
+// (north_star: "tensor cores are not used because this is not a contraction"), so the design
+// rules are: read every log byte exactly once with 128-bit coalesced loads, keep the only
+// random-access structure of the hot loop (the gram filter bitmap) in shared memory, one
+// persistent CTA per SM, no block-wide synchronisation inside the streaming loop.
+//
+//   k_scan        a10 + a11 (hot): newline counts per 2 KiB tile and gram-filter candidates
+//   k_prefix_*    a10: exclusive prefix of the tile counts (the two-level newline index)
+//   k_pods        a10: per-pod line bases
+//   k_confirm     a11: candidate -> exact gram -> literal -> verify DFA on the line -> raw event
+//   k_dfa_scan    a11: combined DFA in shared memory for patterns without a usable literal
+//   sort/unique   ordering + de-duplication of raw events (CUB radix sort, not a hot path)
+//   k_resolve     a12 + a13: line numbers, context ranges, secondary proximity, fp64 score
+//   k_line_starts a10: materialised line table of one pod (ballot/prefix-scan scatter)
+#include <cub/cub.cuh>
+
+#include "pm_kernels.h"
+
+namespace pm {
+
+namespace {
+
+constexpr unsigned FULL = 0xFFFFFFFFu;
+constexpr int kQueue = 64;   // per-warp candidate staging entries
+
+__device__ __forceinline__ uint4 ld_stream16(const uint4 *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+// bit 7 of every byte of the result is set iff that byte of w is NOT '\n' (exact, carry-free)
+__device__ __forceinline__ uint32_t not_newline_flags(uint32_t w) {
+    uint32_t t = (w ^ 0x0A0A0A0Au) & 0x7F7F7F7Fu;
+    return ((t + 0x7F7F7F7Fu) | w) & 0x80808080u;
+}
+
+__device__ __forceinline__ uint32_t newline_mask4(uint32_t w) {   // bit i set iff byte i == '\n'
+    uint32_t x = (~not_newline_flags(w) & 0x80808080u) >> 7;
+    return (x & 1u) | ((x >> 7) & 2u) | ((x >> 14) & 4u) | ((x >> 21) & 8u);
+}
+
+__device__ __forceinline__ uint32_t newline_mask16(const uint4 &v) {
+    return newline_mask4(v.x) | (newline_mask4(v.y) << 4) | (newline_mask4(v.z) << 8) | (newline_mask4(v.w) << 12);
+}
+
+__device__ __forceinline__ unsigned lanemask_lt() {
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// ------------------------------------------------------------------------------------ k_scan
+template <int BITS, bool FOLD>
+__device__ __forceinline__ uint32_t filter_word(uint32_t w, const uint32_t *bm) {
+    uint32_t g = FOLD ? (w | 0x20202020u) : w;
+    uint32_t bit = (g * 0x9E3779B1u) >> (32 - BITS);
+    return (bm[bit >> 5] >> (bit & 31u)) & 1u;
+}
+
+template <int BITS, bool FOLD>
+__global__ void __launch_bounds__(kScanThreads, 1)
+k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g,
+       uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+       ScanCounters *__restrict__ ctr) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int kBitmapWords = (1 << BITS) / 32;
+    uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);
+    unsigned long long *queues = reinterpret_cast<unsigned long long *>(smem_raw + (size_t)kBitmapWords * 4);
+
+    // stage the gram filter: 2^BITS bits, 128-bit copies
+    for (int i = threadIdx.x; i < kBitmapWords / 4; i += blockDim.x) reinterpret_cast<uint4 *>(bm)[i] = bitmap_g[i];
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long *wq = queues + warp * kQueue;
+    int qn = 0;
+    const unsigned long long n_warps = (unsigned long long)gridDim.x * (kScanThreads / 32);
+    const unsigned lt = lanemask_lt();
+
+    for (unsigned long long t = (unsigned long long)blockIdx.x * (kScanThreads / 32) + warp; t < n_tiles; t += n_warps) {
+        const uint4 *base = text + t * (kTileBytes / 16) + lane;
+        uint4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) v[j] = ld_stream16(base + j * 32);   // 4 x 512 B per warp in flight
+        uint32_t nz = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            uint32_t f0 = not_newline_flags(v[j].x), f1 = not_newline_flags(v[j].y);
+            uint32_t f2 = not_newline_flags(v[j].z), f3 = not_newline_flags(v[j].w);
+            nz += __popc(f0 | (f1 >> 1) | (f2 >> 2) | (f3 >> 3));
+            uint32_t m4 = filter_word<BITS, FOLD>(v[j].x, bm) | (filter_word<BITS, FOLD>(v[j].y, bm) << 1) |
+                          (filter_word<BITS, FOLD>(v[j].z, bm) << 2) | (filter_word<BITS, FOLD>(v[j].w, bm) << 3);
+            unsigned b = __ballot_sync(FULL, m4 != 0);
+            if (b) {   // warp-uniform, rare: stage (group, mask) entries, flush 32 at a time
+                if (m4) wq[qn + __popc(b & lt)] = ((t * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
+                qn += __popc(b);
+                __syncwarp();
+                if (qn >= 32) {
+                    unsigned long long at = 0;
+                    if (lane == 0) at = atomicAdd(&ctr->n_cand, 32ull);
+                    at = __shfl_sync(FULL, at, 0);
+                    if (at + 32 <= cand_cap)
+                        cand[at + lane] = wq[lane];
+                    else if (lane == 0)
+                        ctr->cand_overflow = 1;
+                    unsigned long long carry = (lane + 32 < qn) ? wq[lane + 32] : 0ull;
+                    __syncwarp();
+                    qn -= 32;
+                    if (lane < qn) wq[lane] = carry;
+                    __syncwarp();
+                }
+            }
+        }
+        // 16 bytes x 4 loads per lane: newlines = 64 - non-newline bytes
+        uint32_t nl = __reduce_add_sync(FULL, 64u - nz);
+        if (lane == 0) tile_nl[t] = nl;
+    }
+    if (qn > 0) {
+        unsigned long long at = 0;
+        if (lane == 0) at = atomicAdd(&ctr->n_cand, (unsigned long long)qn);
+        at = __shfl_sync(FULL, at, 0);
+        if (at + qn <= cand_cap) {
+            if (lane < qn) cand[at + lane] = wq[lane];
+            if (lane + 32 < qn) cand[at + lane + 32] = wq[lane + 32];
+        } else if (lane == 0) {
+            ctr->cand_overflow = 1;
+        }
+    }
+}
+
+// Newline-only variant: libraries without any filtered pattern still need the tile counts.
+__global__ void __launch_bounds__(kScanThreads, 1)
+k_scan_nl_only(const uint4 *__restrict__ text, unsigned long long n_tiles, uint32_t *__restrict__ tile_nl) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long n_warps = (unsigned long long)gridDim.x * (kScanThreads / 32);
+    for (unsigned long long t = (unsigned long long)blockIdx.x * (kScanThreads / 32) + warp; t < n_tiles; t += n_warps) {
+        const uint4 *base = text + t * (kTileBytes / 16) + lane;
+        uint4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) v[j] = ld_stream16(base + j * 32);
+        uint32_t nz = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            nz += __popc(not_newline_flags(v[j].x) | (not_newline_flags(v[j].y) >> 1) | (not_newline_flags(v[j].z) >> 2) |
+                         (not_newline_flags(v[j].w) >> 3));
+        uint32_t nl = __reduce_add_sync(FULL, 64u - nz);
+        if (lane == 0) tile_nl[t] = nl;
+    }
+}
+
+// ------------------------------------------------------------------------------------ prefix
+constexpr int kPrefThreads = 1024, kPrefItems = 4, kPrefBlock = kPrefThreads * kPrefItems;
+
+__device__ __forceinline__ unsigned long long block_exclusive_scan(unsigned long long v, unsigned long long *total) {
+    __shared__ unsigned long long wsum[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long y = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += y;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long w = wsum[lane], winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long y = __shfl_up_sync(FULL, winc, o);
+            if (lane >= o) winc += y;
+        }
+        wsum[lane] = winc - w;
+        if (lane == 31 && total) *total = winc;
+    }
+    __syncthreads();
+    unsigned long long r = inc - v + wsum[warp];
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(kPrefThreads) k_prefix_partial(const uint32_t *__restrict__ in, unsigned long long n, unsigned long long *__restrict__ block_sums) {
+    unsigned long long i0 = (unsigned long long)blockIdx.x * kPrefBlock + threadIdx.x * kPrefItems, s = 0;
+#pragma unroll
+    for (int k = 0; k < kPrefItems; k++)
+        if (i0 + k < n) s += in[i0 + k];
+    __shared__ unsigned long long tot;
+    block_exclusive_scan(s, &tot);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kPrefThreads) k_prefix_blocks(unsigned long long *block_sums, unsigned long long n_blocks) {
+    __shared__ unsigned long long tot;
+    unsigned long long carry = 0;
+    for (unsigned long long b0 = 0; b0 < n_blocks; b0 += kPrefThreads) {
+        unsigned long long i = b0 + threadIdx.x, v = i < n_blocks ? block_sums[i] : 0;
+        unsigned long long ex = block_exclusive_scan(v, &tot);
+        if (i < n_blocks) block_sums[i] = carry + ex;
+        carry += tot;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kPrefThreads) k_prefix_final(const uint32_t *__restrict__ in, unsigned long long n, const unsigned long long *__restrict__ block_sums,
+                                                                unsigned long long *__restrict__ out) {
+    unsigned long long i0 = (unsigned long long)blockIdx.x * kPrefBlock + threadIdx.x * kPrefItems, s = 0;
+    uint32_t x[kPrefItems];
+#pragma unroll
+    for (int k = 0; k < kPrefItems; k++) {
+        x[k] = (i0 + k < n) ? in[i0 + k] : 0;
+        s += x[k];
+    }
+    unsigned long long ex = block_exclusive_scan(s, nullptr) + block_sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < kPrefItems; k++) {
+        if (i0 + k < n) out[i0 + k] = ex;
+        ex += x[k];
+    }
+}
+
+// ------------------------------------------------------------------------------------ helpers
+// '\n' bytes in text[0, pos): tile prefix + a warp-cooperative recount inside pos's tile.
+__device__ unsigned long long warp_newlines_before(const uint8_t *text, const unsigned long long *tile_prefix, unsigned long long pos) {
+    const int lane = threadIdx.x & 31;
+    unsigned long long tile = pos / kTileBytes, base = tile * kTileBytes;
+    unsigned cnt = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        unsigned long long a = base + k * 512 + lane * 16;
+        if (a < pos) {
+            uint4 v = *reinterpret_cast<const uint4 *>(text + a);
+            uint32_t m = newline_mask16(v);
+            unsigned long long r = pos - a;
+            if (r < 16) m &= (1u << r) - 1u;
+            cnt += __popc(m);
+        }
+    }
+    cnt = __reduce_add_sync(FULL, cnt);
+    return tile_prefix[tile] + cnt;
+}
+
+struct UnitTables {
+    const uint16_t *tab;
+    const uint8_t *cmap;
+    uint32_t stride, accept;
+};
+
+__device__ __forceinline__ UnitTables unit_tables(const uint8_t *blob, const BlobHeader &h, uint32_t unit) {
+    const UnitDesc *u = reinterpret_cast<const UnitDesc *>(blob + h.off_units) + unit;
+    UnitTables t;
+    t.tab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + u->table_off;
+    t.cmap = blob + h.off_classmaps + u->classmap_off;
+    t.stride = u->stride;
+    t.accept = u->accept_state;
+    return t;
+}
+
+// One thread walks one line [a, b) through a verify DFA, then feeds END-OF-LINE.
+__device__ bool line_matches(const uint8_t *text, unsigned long long a, unsigned long long b, const UnitTables &t) {
+    uint32_t s = 0;
+    for (unsigned long long p = a; p < b; p++) {
+        s = t.tab[s * t.stride + t.cmap[text[p]]];
+        if (s == t.accept) return true;
+    }
+    s = t.tab[s * t.stride + t.stride - 1];
+    return s == t.accept;
+}
+
+// ------------------------------------------------------------------------------------ k_pad / k_pods
+__global__ void k_pad(uint8_t *text, const PodDev *pods, const unsigned long long *raw_end, int n_pods, unsigned long long total) {
+    int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w > n_pods) return;
+    // gap w: [raw_end[w-1], start[w]) ; gap 0 is the header, gap n_pods runs to the end of the buffer
+    unsigned long long a = w == 0 ? 0 : raw_end[w - 1], b = w == n_pods ? total : pods[w].start;
+    for (unsigned long long p = a + lane; p < b; p += 32) text[p] = '\n';
+}
+
+__global__ void k_pods(const uint8_t *text, const unsigned long long *tile_prefix, PodDev *pods, int n_pods) {
+    int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= n_pods) return;
+    unsigned long long st = pods[w].start, ee = pods[w].eff_end;
+    unsigned long long c0 = warp_newlines_before(text, tile_prefix, st);
+    unsigned long long c1 = warp_newlines_before(text, tile_prefix, ee);
+    if (lane == 0) {
+        pods[w].nl_before = c0;
+        pods[w].n_lines = ee > st ? (int)(c1 - c0 + 1) : 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------ k_confirm
+__global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h,
+                                                 const unsigned long long *__restrict__ cand, unsigned long long *__restrict__ raw, unsigned long long raw_cap,
+                                                 ScanCounters *ctr) {
+    const unsigned long long n = ctr->n_cand;
+    const uint32_t *gk = reinterpret_cast<const uint32_t *>(blob + h.off_gram_keys);
+    const uint32_t *gf = reinterpret_cast<const uint32_t *>(blob + h.off_gram_first);
+    const uint32_t *gc = reinterpret_cast<const uint32_t *>(blob + h.off_gram_count);
+    const Probe *probes = reinterpret_cast<const Probe *>(blob + h.off_probes);
+    const uint8_t *litpool = blob + h.off_litpool;
+    const PatternDesc *pd = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
+    const uint32_t cap_mask = (1u << h.gram_log2_cap) - 1u;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned long long e = cand[i];
+        unsigned long long group = e >> 4;
+        uint32_t m4 = (uint32_t)(e & 15u);
+        while (m4) {
+            int k = __ffs(m4) - 1;
+            m4 &= m4 - 1;
+            unsigned long long p = group * 16 + k * 4;
+            uint32_t g = *reinterpret_cast<const uint32_t *>(text + p);
+            if (h.filter_fold) g |= 0x20202020u;
+            uint32_t slot = gram_table_slot(g, h.gram_log2_cap);
+            uint32_t key;
+            while ((key = gk[slot]) != g && key != kGramEmpty) slot = (slot + 1) & cap_mask;
+            if (key != g) continue;   // bitmap collision
+            for (uint32_t q = gf[slot], qe = q + gc[slot]; q < qe; q++) {
+                Probe pr = probes[q];
+                if (p < kHeaderBytes + pr.gram_off) continue;
+                unsigned long long st = p - pr.gram_off;
+                if (st + pr.lit_len > total) continue;
+                const uint8_t *lit = litpool + pr.lit_off, *msk = lit + pr.lit_len;
+                bool eq = true;
+                for (uint32_t j = 0; j < pr.lit_len; j++)
+                    if ((uint8_t)(text[st + j] | msk[j]) != lit[j]) {
+                        eq = false;
+                        break;
+                    }
+                if (!eq) continue;
+                atomicAdd(&ctr->n_verified, 1ull);
+                // the line that holds the gram
+                unsigned long long ls = p, le = p;
+                while (text[ls - 1] != '\n') ls--;
+                while (text[le] != '\n') le++;
+                unsigned long long lend = (le > ls && text[le - 1] == '\r') ? le - 1 : le;
+                UnitTables ut = unit_tables(blob, h, pd[pr.pattern].unit);
+                if (line_matches(text, ls, lend, ut)) {
+                    unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
+                    if (at < raw_cap)
+                        raw[at] = (ls << kPatternBits) | pr.pattern;
+                    else
+                        ctr->raw_overflow = 1;
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ k_dfa_scan
+// Combined search DFA of the patterns that have no 7-byte literal.  Transition table and class
+// map live in shared memory; every thread owns the lines that START inside its chunk and keeps
+// walking past the chunk end until that last line is finished (overlapping chunks), so no
+// state crosses threads.  Correctness first: text is read through L1 here; the filter path
+// above is the one built for bandwidth.
+constexpr int kDfaThreads = 256, kDfaChunk = 256;
+
+__global__ void __launch_bounds__(kDfaThreads) k_dfa_scan(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h, int group,
+                                                          unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const GroupDesc gd = reinterpret_cast<const GroupDesc *>(blob + h.off_groups)[group];
+    const uint16_t *gtab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + gd.table_off;
+    const uint8_t *gcm = blob + h.off_classmaps + gd.classmap_off;
+    const uint32_t *acc = reinterpret_cast<const uint32_t *>(blob + h.off_group_accept) + gd.accept_off;
+    uint8_t *cmap = smem_raw;
+    uint16_t *tab = reinterpret_cast<uint16_t *>(smem_raw + 256);
+    const uint32_t n_entries = (uint32_t)gd.nstates * gd.stride;
+    for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) cmap[i] = gcm[i];
+    for (uint32_t i = threadIdx.x; i < n_entries; i += blockDim.x) tab[i] = gtab[i];
+    __syncthreads();
+    const uint32_t stride = gd.stride, first_accept = gd.first_accept;
+    const unsigned long long n_chunks = (total - kHeaderBytes + kDfaChunk - 1) / kDfaChunk;
+    for (unsigned long long c = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; c < n_chunks; c += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned long long cb = kHeaderBytes + c * kDfaChunk, ce = cb + kDfaChunk;
+        if (ce > total) ce = total;
+        // first line start in [cb, ce): the byte after the first '\n' at position >= cb - 1
+        unsigned long long p = cb - 1;
+        while (p < ce && text[p] != '\n') p++;
+        p++;
+        while (p < ce) {   // p is a line start inside the chunk
+            unsigned long long ls = p;
+            uint32_t s = 0, last_emit = 0xFFFFFFFFu;
+            for (;;) {
+                uint8_t b = text[p];
+                // a line ends at '\n', or at the '\r' of a "\r\n" separator (SPEC.md section 2)
+                bool crlf = (b == '\r') && text[p + 1] == '\n';
+                bool eol = (b == '\n') || crlf;
+                if (crlf) p++;
+                s = tab[s * stride + (eol ? stride - 1 : cmap[b])];
+                if (s >= first_accept && s != last_emit) {
+                    last_emit = s;
+                    uint32_t a0 = acc[s - first_accept], a1 = acc[s - first_accept + 1];
+                    for (uint32_t k = a0; k < a1; k++) {
+                        unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
+                        if (at < raw_cap)
+                            raw[at] = (ls << kPatternBits) | acc[k];
+                        else
+                            ctr->raw_overflow = 1;
+                    }
+                }
+                p++;
+                if (eol) break;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ unique
+__global__ void k_mark_unique(const unsigned long long *sorted, unsigned long long n, unsigned char *flags) {
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = (sorted[i] != ~0ull) && (i == 0 || sorted[i] != sorted[i - 1]);
+}
+
+// ------------------------------------------------------------------------------------ k_resolve
+constexpr int kResolveWarps = 2;
+constexpr int kCtxSlots = kMaxCtxLines + 2;
+
+// Collects positions of the next `need` '\n' bytes at positions >= from into out[0..need).
+__device__ void warp_collect_forward(const uint8_t *text, unsigned long long from, int need, unsigned long long *out) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = lanemask_lt();
+    unsigned long long a0 = from & ~15ull;
+    int got = 0;
+    while (got < need) {
+        unsigned long long a = a0 + (unsigned long long)lane * 16;
+        uint4 v = *reinterpret_cast<const uint4 *>(text + a);
+        uint32_t m = newline_mask16(v);
+        if (a < from) m &= (from - a >= 16) ? 0u : ~((1u << (from - a)) - 1u);
+        int c = __popc(m);
+        // exclusive prefix over lanes via ballots of the counts' bits is overkill: use shfl scan
+        int inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += y;
+        }
+        int rank = got + inc - c;
+        while (m && rank < need) {
+            int bpos = __ffs(m) - 1;
+            m &= m - 1;
+            out[rank++] = a + bpos;
+        }
+        got += __shfl_sync(FULL, inc, 31);
+        a0 += 512;
+        (void)lt;
+    }
+    __syncwarp();
+}
+
+// Collects positions of the previous `need` '\n' bytes at positions < before into out[0..need),
+// nearest first.
+__device__ void warp_collect_backward(const uint8_t *text, unsigned long long before, int need, unsigned long long *out) {
+    const int lane = threadIdx.x & 31;
+    unsigned long long top = (before + 15) & ~15ull;   // first 16-byte boundary >= before
+    int got = 0;
+    while (got < need) {
+        long long a = (long long)top - 16ll * (lane + 1);
+        uint32_t m = 0;
+        if (a >= 0) {
+            uint4 v = *reinterpret_cast<const uint4 *>(text + a);
+            m = newline_mask16(v);
+            if ((unsigned long long)a + 16 > before) m &= (1u << (before - (unsigned long long)a)) - 1u;
+        }
+        int c = __popc(m);
+        int inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(FULL, inc, o);
+            if (lane >= o) inc += y;
+        }
+        int rank = got + inc - c;
+        while (m && rank < need) {
+            int bpos = 31 - __clz(m);
+            m &= ~(1u << bpos);
+            out[rank++] = (unsigned long long)a + bpos;
+        }
+        got += __shfl_sync(FULL, inc, 31);
+        if (top < 512) break;
+        top -= 512;
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(kResolveWarps * 32) k_resolve(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
+                                                                const unsigned long long *__restrict__ tile_prefix, const PodDev *__restrict__ pods, int n_pods,
+                                                                const unsigned long long *__restrict__ uniq, unsigned long long n_events, EventOut out) {
+    __shared__ unsigned long long fwd_s[kResolveWarps][kCtxSlots];   // fwd[i]: '\n' that ends line L+i
+    __shared__ unsigned long long bwd_s[kResolveWarps][kCtxSlots];   // bwd[i]: '\n' that precedes line L-i
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long *fwd = fwd_s[warp], *bwd = bwd_s[warp];
+    const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
+    const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
+
+    for (unsigned long long ev = (unsigned long long)blockIdx.x * kResolveWarps + warp; ev < n_events; ev += (unsigned long long)gridDim.x * kResolveWarps) {
+        const unsigned long long key = uniq[ev], ls = key >> kPatternBits;
+        const uint32_t pat = (uint32_t)(key & ((1u << kPatternBits) - 1u));
+        const PatternDesc pd = pds[pat];
+        // pod = last pod with start <= ls
+        int lo = 0, hi = n_pods - 1;
+        while (lo < hi) {
+            int mid = (lo + hi + 1) >> 1;
+            if (pods[mid].start <= ls) lo = mid; else hi = mid - 1;
+        }
+        const PodDev pod = pods[lo];
+        const long long L = (long long)(warp_newlines_before(text, tile_prefix, ls) - pod.nl_before) + 1;
+        const long long n_lines = pod.n_lines;
+        const int nb = (int)min((long long)pd.lines_before, L - 1);
+        const int na = (int)min((long long)pd.lines_after, n_lines - L);
+        int need_f = na, need_b = nb;
+        if (pd.include_stack) need_f = max(need_f, (int)min((long long)kStackMax, n_lines - L));
+        for (uint32_t j = 0; j < pd.sec_count; j++) {
+            int w = sds[pd.sec_first + j].window;
+            need_f = max(need_f, (int)min((long long)w, n_lines - L));
+            need_b = max(need_b, (int)min((long long)w, L - 1));
+        }
+        warp_collect_forward(text, ls, need_f + 1, fwd);
+        if (lane == 0) bwd[0] = ls - 1;
+        if (need_b > 0) warp_collect_backward(text, ls - 1, need_b, bwd + 1);
+        __syncwarp();
+
+        auto line_span = [&](int rel, unsigned long long &a, unsigned long long &b) {   // rel: line L+rel
+            if (rel >= 0) {
+                a = rel == 0 ? ls : fwd[rel - 1] + 1;
+                b = fwd[rel];
+            } else {
+                a = bwd[-rel] + 1;
+                b = bwd[-rel - 1];
+            }
+            if (b > a && text[b - 1] == '\r') b--;
+        };
+
+        // ---- context (a13)
+        int last_rel = na;
+        if (pd.include_stack && na < kStackMax) {
+            const int cap_rel = (int)min((long long)kStackMax, n_lines - L);
+            UnitTables st = unit_tables(blob, h, h.stack_unit);
+            // lines L+na+1 .. L+cap_rel, 32 at a time; stop at the first non-stack line
+            for (int r0 = na + 1; r0 <= cap_rel; r0 += 32) {
+                int rel = r0 + lane;
+                bool ok = false;
+                if (rel <= cap_rel) {
+                    unsigned long long a, b;
+                    line_span(rel, a, b);
+                    ok = line_matches(text, a, b, st);
+                }
+                unsigned good = __ballot_sync(FULL, ok);
+                int run = __ffs(~good) - 1;   // leading lanes that are stack lines (32 if all)
+                if (run < 0) run = 32;
+                int avail = min(32, cap_rel - r0 + 1);
+                run = min(run, avail);
+                last_rel = r0 + run - 1;
+                if (run < 32) break;
+            }
+            last_rel = max(last_rel, na);
+        }
+        // ---- score (a12): secondaries in order, nearest matching line within the window
+        double acc = 0.0;
+        for (uint32_t j = 0; j < pd.sec_count; j++) {
+            const SecDesc sd = sds[pd.sec_first + j];
+            UnitTables ut = unit_tables(blob, h, sd.unit);
+            int best = 0x7FFFFFFF;
+            for (int i0 = 0; i0 < 2 * sd.window + 1; i0 += 32) {
+                int idx = i0 + lane;
+                if (idx < 2 * sd.window + 1) {
+                    int d = (idx + 1) >> 1;
+                    int rel = (idx & 1) ? -d : d;
+                    bool valid = rel >= 0 ? (d <= n_lines - L) : (d <= L - 1);
+                    if (valid && d < best) {
+                        unsigned long long a, b;
+                        line_span(rel, a, b);
+                        if (line_matches(text, a, b, ut)) best = d;
+                    }
+                }
+                int wbest = __reduce_min_sync(FULL, best);
+                if (wbest != 0x7FFFFFFF) {   // distances only grow with i0
+                    best = wbest;
+                    break;
+                }
+            }
+            best = __reduce_min_sync(FULL, best);
+            if (best != 0x7FFFFFFF) {
+                double term = __dmul_rn(sd.weight, __dsub_rn(1.0, __ddiv_rn((double)best, (double)(sd.window + 1))));
+                acc = __dadd_rn(acc, term);
+            }
+        }
+        if (lane == 0) {
+            unsigned long long la, lb, ca, cb, ea, eb;
+            line_span(0, la, lb);
+            line_span(-nb, ca, cb);
+            line_span(last_rel, ea, eb);
+            out.pod[ev] = lo;
+            out.pattern[ev] = (int32_t)pat;
+            out.line_no[ev] = (int32_t)L;
+            out.line_start[ev] = (int64_t)(ls - pod.start);
+            out.line_len[ev] = (int32_t)(lb - la);
+            out.ctx_first[ev] = (int32_t)(L - nb);
+            out.ctx_last[ev] = (int32_t)(L + last_rel);
+            out.ctx_start[ev] = (int64_t)(ca - pod.start);
+            out.ctx_end[ev] = (int64_t)(eb - pod.start);
+            out.score[ev] = __dmul_rn(__dmul_rn(pd.confidence, pd.mult), __dadd_rn(1.0, acc));
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------ k_line_starts
+// Materialised newline index of one pod (a10): out[r] = offset of line r relative to the pod.
+// One warp per 2 KiB tile: 16-bit newline masks per lane, warp prefix scan of the popcounts,
+// scatter at tile_prefix[tile] - nl_before(pod) + rank + 1.
+__global__ void __launch_bounds__(256) k_line_starts(const uint8_t *__restrict__ text, const unsigned long long *__restrict__ tile_prefix, unsigned long long nl_before,
+                                                     int n_lines, unsigned long long pod_start, unsigned long long pod_eff_end, long long *__restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const unsigned long long first_tile = pod_start / kTileBytes, last_tile = (pod_eff_end + kTileBytes - 1) / kTileBytes;
+    const unsigned long long n_warps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n_lines > 0) out[0] = 0;
+    for (unsigned long long t = first_tile + (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); t < last_tile; t += n_warps) {
+        unsigned long long base = t * kTileBytes;
+        long long rank0 = (long long)tile_prefix[t] - (long long)nl_before;   // newlines of the pod before this tile
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            unsigned long long a = base + k * 512 + lane * 16;
+            uint4 v = *reinterpret_cast<const uint4 *>(text + a);
+            uint32_t m = newline_mask16(v);
+            int c = __popc(m), inc = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(FULL, inc, o);
+                if (lane >= o) inc += y;
+            }
+            long long r = rank0 + inc - c;
+            while (m) {
+                int bpos = __ffs(m) - 1;
+                m &= m - 1;
+                unsigned long long pos = a + bpos;
+                // newline number r (0-based within the pod) ends line r and starts line r + 1
+                if (pos >= pod_start && r + 1 < n_lines && r >= 0) out[r + 1] = (long long)(pos + 1 - pod_start);
+                r++;
+            }
+            rank0 += __shfl_sync(FULL, inc, 31);
+        }
+    }
+}
+
+template <int BITS>
+cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, uint32_t *tile_nl, unsigned long long *cand,
+                             unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
+    cudaError_t e;
+    if (fold) {
+        e = cudaFuncSetAttribute(k_scan<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
+    } else {
+        e = cudaFuncSetAttribute(k_scan<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_pad(uint8_t *text, const PodDev *pods, const unsigned long long *pod_raw_end, int n_pods, unsigned long long total_bytes, cudaStream_t s) {
+    int warps = n_pods + 1, threads = 128, blocks = (warps * 32 + threads - 1) / threads;
+    k_pad<<<blocks, threads, 0, s>>>(text, pods, pod_raw_end, n_pods, total_bytes);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const DeviceLibrary &lib, uint32_t *tile_nl, unsigned long long *cand,
+                        unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    const BlobHeader &h = lib.h;
+    if (h.filter_log2_bits == 0) {
+        k_scan_nl_only<<<num_sms, kScanThreads, 0, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, tile_nl);
+        return cudaGetLastError();
+    }
+    const uint4 *bitmap = reinterpret_cast<const uint4 *>(lib.blob + h.off_bitmap);
+    switch (h.filter_log2_bits) {
+        case 15: return launch_scan_bits<15>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 16: return launch_scan_bits<16>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 17: return launch_scan_bits<17>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 18: return launch_scan_bits<18>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 19: return launch_scan_bits<19>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 20: return launch_scan_bits<20>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+cudaError_t launch_prefix(const uint32_t *tile_nl, unsigned long long *tile_prefix, unsigned long long n_tiles, unsigned long long *scratch, cudaStream_t s) {
+    unsigned long long n_blocks = (n_tiles + kPrefBlock - 1) / kPrefBlock;
+    if (n_blocks == 0) return cudaSuccess;
+    k_prefix_partial<<<(unsigned)n_blocks, kPrefThreads, 0, s>>>(tile_nl, n_tiles, scratch);
+    k_prefix_blocks<<<1, kPrefThreads, 0, s>>>(scratch, n_blocks);
+    k_prefix_final<<<(unsigned)n_blocks, kPrefThreads, 0, s>>>(tile_nl, n_tiles, scratch, tile_prefix);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_prefix, PodDev *pods, int n_pods, cudaStream_t s) {
+    if (n_pods == 0) return cudaSuccess;
+    int threads = 128, blocks = (n_pods * 32 + threads - 1) / threads;
+    k_pods<<<blocks, threads, 0, s>>>(text, tile_prefix, pods, n_pods);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, const unsigned long long *cand, unsigned long long *raw,
+                           unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    if (lib.h.filter_log2_bits == 0) return cudaSuccess;
+    k_confirm<<<num_sms * 4, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, cand, raw, raw_cap, ctr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, int group, unsigned long long *raw,
+                            unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    // host copy of the group's size is not kept: budget the shared memory for the compiler's limit
+    size_t smem = 256 + 96 * 1024;
+    cudaError_t e = cudaFuncSetAttribute(k_dfa_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_dfa_scan<<<num_sms * 2, kDfaThreads, smem, s>>>(text, total_bytes, lib.blob, lib.h, group, raw, raw_cap, ctr);
+    return cudaGetLastError();
+}
+
+size_t sort_temp_bytes(unsigned long long n) {
+    size_t a = 0, b = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, a, (const unsigned long long *)nullptr, (unsigned long long *)nullptr, (long long)n);
+    cub::DeviceSelect::Flagged(nullptr, b, (const unsigned long long *)nullptr, (const unsigned char *)nullptr, (unsigned long long *)nullptr,
+                               (unsigned long long *)nullptr, (long long)n);
+    return ((a > b ? a : b) + 255) / 256 * 256 + ((n + 255) / 256) * 256;   // + flag bytes
+}
+
+cudaError_t launch_sort_unique(unsigned long long *raw, unsigned long long *sorted, unsigned long long *uniq, unsigned long long n, unsigned long long *n_unique,
+                               void *temp, size_t temp_bytes, cudaStream_t s) {
+    if (n == 0) return cudaMemsetAsync(n_unique, 0, sizeof(unsigned long long), s);
+    size_t flag_bytes = ((n + 255) / 256) * 256;
+    unsigned char *flags = reinterpret_cast<unsigned char *>(temp);
+    void *cub_temp = flags + flag_bytes;
+    size_t cub_bytes = temp_bytes - flag_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortKeys(cub_temp, cub_bytes, raw, sorted, (long long)n, 0, 64, s);
+    if (e != cudaSuccess) return e;
+    k_mark_unique<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(sorted, n, flags);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    return cub::DeviceSelect::Flagged(cub_temp, cub_bytes, sorted, flags, uniq, n_unique, (long long)n, s);
+}
+
+cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, const PodDev *pods, int n_pods,
+                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, cudaStream_t s) {
+    if (n_events == 0) return cudaSuccess;
+    unsigned blocks = (unsigned)((n_events + kResolveWarps - 1) / kResolveWarps);
+    if (blocks > 148u * 16u) blocks = 148u * 16u;
+    k_resolve<<<blocks, kResolveWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pods, n_pods, uniq, n_events, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_line_starts(const uint8_t *text, const unsigned long long *tile_prefix, unsigned long long nl_before, int n_lines,
+                                  unsigned long long pod_start, unsigned long long pod_eff_end, long long *out, int num_sms, cudaStream_t s) {
+    k_line_starts<<<num_sms * 2, 256, 0, s>>>(text, tile_prefix, nl_before, n_lines, pod_start, pod_eff_end, out);
+    return cudaGetLastError();
+}
+
+}  // namespace pm

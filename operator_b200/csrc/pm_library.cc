@@ -186,7 +186,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
                     const JsonValue *st = ctx->get("include_stack_trace");
                     if (st && st->type == JsonValue::Bool) d.include_stack = st->b;
                 }
-                if (d.lines_before < 0 || d.lines_after < 0 || d.lines_before > 100000 || d.lines_after > 100000)
+                if (d.lines_before < 0 || d.lines_after < 0 || d.lines_before > 1000 || d.lines_after > 1000)
                     throw CompileFail{PM_E_SYNTAX, idx, -1, -1, pi.id, "context_extraction out of range"};
 
                 // primary regex -> verify DFA (+ AST kept for literal analysis / grouping)
@@ -212,7 +212,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
                         double v;
                         if (num_of(s.get("weight"), v)) sd.weight = v;
                         if (num_of(s.get("proximity_window"), v)) sd.window = (int32_t)v;
-                        if (sd.window < 0 || sd.window > 10000)
+                        if (sd.window < 0 || sd.window > 1000)
                             throw CompileFail{PM_E_SYNTAX, idx, j, -1, pi.id, "proximity_window out of range"};
                         sd.unit = (uint32_t)units.size();
                         units.emplace_back();

@@ -1,0 +1,782 @@
+// Host runtime behind the C ABI (include/podmortem_scan.h): context, device memory pool,
+// library publication, pod batches with pod-level sharding over the GPUs of one node, and the
+// marshalling of device results into pinned structure-of-arrays views.
+//
+// Reference side of this boundary: LogParserRestClient.parseLogs (LogParserRestClient.java:37-39)
+// carries one pod per request (PodFailureWatcher.java:196-199); a batch is what the new /parse
+// resource submits after coalescing concurrent requests.  Pods are
+// independent, so the multi-GPU path is a partition of the pods (longest-processing-time greedy
+// by bytes) with no collective; match lists are gathered on the host.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "pm_kernels.h"
+#include "pm_library.h"
+#include "podmortem_scan.h"
+
+using namespace pm;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int status, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return status;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) return fail(PM_E_CUDA, "%s: %s", #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+struct Pool {   // size-bucketed free list; blocks are handed back, never split
+    std::mutex mu;
+    std::multimap<size_t, void *> free_blocks;
+    bool pinned = false;
+    int device = 0;
+
+    int get(size_t bytes, void **out, size_t *cap) {
+        if (bytes == 0) bytes = 256;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            auto it = free_blocks.lower_bound(bytes);
+            if (it != free_blocks.end() && it->first <= bytes * 4 + (1u << 20)) {
+                *out = it->second;
+                *cap = it->first;
+                free_blocks.erase(it);
+                return PM_OK;
+            }
+        }
+        size_t want = (bytes + 255) & ~(size_t)255;
+        cudaError_t e;
+        if (pinned) {
+            e = cudaHostAlloc(out, want, cudaHostAllocPortable);
+        } else {
+            cudaSetDevice(device);
+            e = cudaMalloc(out, want);
+        }
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            trim();
+            e = pinned ? cudaHostAlloc(out, want, cudaHostAllocPortable) : cudaMalloc(out, want);
+            if (e != cudaSuccess) return fail(PM_E_NOMEM, "%s of %zu bytes: %s", pinned ? "cudaHostAlloc" : "cudaMalloc", want, cudaGetErrorString(e));
+        }
+        *cap = want;
+        return PM_OK;
+    }
+    void put(void *p, size_t cap) {
+        if (!p) return;
+        std::lock_guard<std::mutex> g(mu);
+        free_blocks.emplace(cap, p);
+    }
+    void trim() {
+        std::lock_guard<std::mutex> g(mu);
+        for (auto &kv : free_blocks) pinned ? cudaFreeHost(kv.second) : cudaFree(kv.second);
+        free_blocks.clear();
+    }
+};
+
+struct Buf {
+    void *p = nullptr;
+    size_t cap = 0;
+    template <class T>
+    T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct Device {
+    int id = 0, num_sms = 0;
+    Pool pool;
+    std::mutex busy;   // one batch pipeline at a time per device
+};
+
+}  // namespace
+
+struct pm_library {
+    CompiledLibrary lib;
+    std::atomic<int> refs{1};
+    std::vector<DeviceLibrary> dev;   // per context device, after publish
+    std::vector<void *> dev_blobs;
+    pm_ctx *owner = nullptr;
+};
+
+struct pm_ctx {
+    std::vector<Device *> devs;
+    Pool pinned;
+    std::mutex mu;
+    pm_library *current = nullptr;
+    std::mutex user_pinned_mu;
+    std::map<void *, size_t> user_pinned;
+    std::string parse_response;   // see pm_service.cc
+};
+
+namespace {
+
+void lib_unref(pm_library *l) {
+    if (!l) return;
+    if (l->refs.fetch_sub(1) == 1) {
+        for (size_t d = 0; d < l->dev_blobs.size(); d++)
+            if (l->dev_blobs[d]) {
+                cudaSetDevice(l->owner->devs[d]->id);
+                cudaFree(l->dev_blobs[d]);
+            }
+        delete l;
+    }
+}
+
+struct PodRef {
+    const uint8_t *ptr;
+    size_t len, eff_len;
+    uint64_t tag;
+    int dev = 0, local = 0;   // device slot and index among that device's pods
+    uint64_t start = 0;       // offset in the device text buffer
+};
+
+struct DevWork {
+    int slot = -1;   // index into ctx->devs
+    std::vector<int> pods;   // batch pod indices, ascending
+    uint64_t total = 0, n_tiles = 0;
+    uint64_t cand_cap = 0, raw_cap = 0;
+    Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, raw_end, ev_soa, lines_tmp;
+    Buf h_ctr, h_pods, h_soa;   // pinned mirrors
+    cudaStream_t stream = nullptr;
+    cudaEvent_t e[8] = {nullptr};   // 0 h2d0, 1 h2d1, 2 scan0, 3 scan1, 4 mid, 5 post0, 6 post1, 7 d2h1
+    uint64_t n_events = 0, n_cand = 0, n_verified = 0;
+    bool locked = false, staged = false, scanned = false;
+    int launches = 0;
+};
+
+size_t round_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Length without trailing "\r?\n" separators (Java split drops trailing empty strings).
+size_t effective_len(const uint8_t *p, size_t n) {
+    while (n > 0 && p[n - 1] == '\n') {
+        n--;
+        if (n > 0 && p[n - 1] == '\r') n--;
+    }
+    return n;
+}
+
+}  // namespace
+
+struct pm_batch {
+    pm_ctx *ctx = nullptr;
+    pm_library *lib = nullptr;
+    std::vector<PodRef> pods;
+    std::vector<DevWork> work;
+    bool staged = false, submitted = false;
+    // final result (pinned, batch order)
+    Buf r_soa, r_pod;
+    pm_result_view view;
+    std::vector<int32_t> pod_n_lines;
+};
+
+namespace {
+
+int get(Pool &p, size_t bytes, Buf &b) {
+    if (b.p && b.cap >= bytes) return PM_OK;
+    if (b.p) p.put(b.p, b.cap);
+    b.p = nullptr;
+    b.cap = 0;
+    return p.get(bytes, &b.p, &b.cap);
+}
+void put(Pool &p, Buf &b) {
+    p.put(b.p, b.cap);
+    b.p = nullptr;
+    b.cap = 0;
+}
+
+void release_work(pm_batch *b) {
+    for (auto &w : b->work) {
+        Device *d = b->ctx->devs[w.slot];
+        cudaSetDevice(d->id);
+        if (w.stream) cudaStreamSynchronize(w.stream);
+        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.raw_end, &w.ev_soa, &w.lines_tmp})
+            put(d->pool, *x);
+        for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa}) put(b->ctx->pinned, *x);
+        for (auto &ev : w.e)
+            if (ev) cudaEventDestroy(ev), ev = nullptr;
+        if (w.stream) cudaStreamDestroy(w.stream), w.stream = nullptr;
+        if (w.locked) d->busy.unlock(), w.locked = false;
+    }
+    b->work.clear();
+}
+
+// SoA layout of n events inside one allocation (8-byte fields first)
+struct SoaLayout {
+    size_t off_line_start, off_ctx_start, off_ctx_end, off_score, off_pod, off_pattern, off_line_no, off_line_len, off_ctx_first, off_ctx_last, bytes;
+    explicit SoaLayout(uint64_t n) {
+        size_t n8 = round_up(n * 8, 64), n4 = round_up(n * 4, 64);
+        off_line_start = 0;
+        off_ctx_start = n8;
+        off_ctx_end = 2 * n8;
+        off_score = 3 * n8;
+        off_pod = 4 * n8;
+        off_pattern = off_pod + n4;
+        off_line_no = off_pattern + n4;
+        off_line_len = off_line_no + n4;
+        off_ctx_first = off_line_len + n4;
+        off_ctx_last = off_ctx_first + n4;
+        bytes = off_ctx_last + n4 + 64;
+    }
+    EventOut on(void *base) const {
+        char *b = reinterpret_cast<char *>(base);
+        EventOut o;
+        o.line_start = reinterpret_cast<int64_t *>(b + off_line_start);
+        o.ctx_start = reinterpret_cast<int64_t *>(b + off_ctx_start);
+        o.ctx_end = reinterpret_cast<int64_t *>(b + off_ctx_end);
+        o.score = reinterpret_cast<double *>(b + off_score);
+        o.pod = reinterpret_cast<int32_t *>(b + off_pod);
+        o.pattern = reinterpret_cast<int32_t *>(b + off_pattern);
+        o.line_no = reinterpret_cast<int32_t *>(b + off_line_no);
+        o.line_len = reinterpret_cast<int32_t *>(b + off_line_len);
+        o.ctx_first = reinterpret_cast<int32_t *>(b + off_ctx_first);
+        o.ctx_last = reinterpret_cast<int32_t *>(b + off_ctx_last);
+        return o;
+    }
+};
+
+int stage(pm_batch *b) {
+    pm_ctx *ctx = b->ctx;
+    if (b->staged) return PM_OK;
+    {
+        std::lock_guard<std::mutex> g(ctx->mu);
+        if (!ctx->current) return fail(PM_E_NO_LIBRARY, "no pattern library published");
+        b->lib = ctx->current;
+        b->lib->refs.fetch_add(1);
+    }
+    const int nd = (int)ctx->devs.size();
+    // ---- pod -> device: longest-processing-time greedy by bytes
+    std::vector<int> order(b->pods.size());
+    for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return b->pods[x].len > b->pods[y].len; });
+    std::vector<uint64_t> load(nd, 0);
+    for (int i : order) {
+        int best = 0;
+        for (int d = 1; d < nd; d++)
+            if (load[d] < load[best]) best = d;
+        b->pods[i].dev = best;
+        load[best] += b->pods[i].len + 64;
+    }
+    b->work.clear();
+    std::vector<int> slot_of(nd, -1);
+    for (size_t i = 0; i < b->pods.size(); i++) {
+        int d = b->pods[i].dev;
+        if (slot_of[d] < 0) {
+            slot_of[d] = (int)b->work.size();
+            b->work.emplace_back();
+            b->work.back().slot = d;
+        }
+        DevWork &w = b->work[slot_of[d]];
+        b->pods[i].local = (int)w.pods.size();
+        w.pods.push_back((int)i);
+    }
+    // ---- per device: layout, buffers, copies
+    for (auto &w : b->work) {
+        Device *d = ctx->devs[w.slot];
+        d->busy.lock();
+        w.locked = true;
+        CU(cudaSetDevice(d->id));
+        CU(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+        for (auto &ev : w.e) CU(cudaEventCreate(&ev));
+        const int np = (int)w.pods.size();
+        uint64_t off = kHeaderBytes;
+        int rc;
+        if ((rc = get(ctx->pinned, sizeof(PodDev) * (np + 1) + 8 * (np + 1), w.h_pods))) return rc;
+        PodDev *hp = w.h_pods.as<PodDev>();
+        unsigned long long *hre = reinterpret_cast<unsigned long long *>(hp + np + 1);
+        for (int k = 0; k < np; k++) {
+            PodRef &p = b->pods[w.pods[k]];
+            p.start = off;
+            hp[k].start = off;
+            hp[k].eff_end = off + p.eff_len;
+            hp[k].nl_before = 0;
+            hp[k].n_lines = 0;
+            hre[k] = off + p.len;
+            off = round_up(off + p.len + 1, 16);   // >= 1 byte of '\n' padding
+        }
+        // content end, rounded to a tile, plus one full tile of '\n' so that 512-byte look-ahead
+        // reads of the context collector stay inside the buffer
+        w.total = round_up(off, kTileBytes) + kTileBytes;
+        w.n_tiles = w.total / kTileBytes;
+        if (w.total >= (1ull << 40)) return fail(PM_E_INVALID, "more than 1 TiB of log text on one device");
+        w.cand_cap = std::max<uint64_t>(1u << 20, w.total / 256);
+        w.raw_cap = std::max<uint64_t>(1u << 18, w.total / 1024);
+        if ((rc = get(d->pool, w.total, w.text))) return rc;
+        if ((rc = get(d->pool, w.n_tiles * 4, w.tile_nl))) return rc;
+        if ((rc = get(d->pool, w.n_tiles * 8, w.tile_prefix))) return rc;
+        if ((rc = get(d->pool, (w.n_tiles / 4096 + 2) * 8, w.scratch))) return rc;
+        if ((rc = get(d->pool, w.cand_cap * 8, w.cand))) return rc;
+        if ((rc = get(d->pool, w.raw_cap * 8, w.raw))) return rc;
+        if ((rc = get(d->pool, sizeof(ScanCounters) + 64, w.ctr))) return rc;
+        if ((rc = get(d->pool, sizeof(PodDev) * (np + 1), w.pods_dev))) return rc;
+        if ((rc = get(d->pool, 8 * (np + 1), w.raw_end))) return rc;
+        if ((rc = get(ctx->pinned, sizeof(ScanCounters) + 64, w.h_ctr))) return rc;
+        CU(cudaMemcpyAsync(w.pods_dev.p, hp, sizeof(PodDev) * np, cudaMemcpyHostToDevice, w.stream));
+        CU(cudaMemcpyAsync(w.raw_end.p, hre, 8 * np, cudaMemcpyHostToDevice, w.stream));
+        CU(cudaEventRecord(w.e[0], w.stream));
+        for (int k = 0; k < np; k++) {
+            PodRef &p = b->pods[w.pods[k]];
+            if (p.len) CU(cudaMemcpyAsync(w.text.as<uint8_t>() + p.start, p.ptr, p.len, cudaMemcpyHostToDevice, w.stream));
+        }
+        CU(cudaEventRecord(w.e[1], w.stream));
+        CU(launch_pad(w.text.as<uint8_t>(), w.pods_dev.as<PodDev>(), w.raw_end.as<unsigned long long>(), np, w.total, w.stream));
+        w.launches = 1;
+        w.staged = true;
+    }
+    b->staged = true;
+    return PM_OK;
+}
+
+int scan_async(pm_batch *b) {
+    pm_ctx *ctx = b->ctx;
+    for (auto &w : b->work) {
+        Device *d = ctx->devs[w.slot];
+        CU(cudaSetDevice(d->id));
+        const DeviceLibrary &dl = b->lib->dev[w.slot];
+        const int np = (int)w.pods.size();
+        CU(cudaMemsetAsync(w.ctr.p, 0, sizeof(ScanCounters), w.stream));
+        CU(cudaEventRecord(w.e[2], w.stream));
+        CU(launch_scan(w.text.as<uint8_t>(), w.n_tiles, dl, w.tile_nl.as<uint32_t>(), w.cand.as<unsigned long long>(), w.cand_cap,
+                       w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
+        CU(cudaEventRecord(w.e[3], w.stream));
+        CU(launch_prefix(w.tile_nl.as<uint32_t>(), w.tile_prefix.as<unsigned long long>(), w.n_tiles, w.scratch.as<unsigned long long>(), w.stream));
+        CU(launch_pods(w.text.as<uint8_t>(), w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), np, w.stream));
+        CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.cand.as<unsigned long long>(), w.raw.as<unsigned long long>(), w.raw_cap,
+                          w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
+        w.launches += 1 + 3 + (np ? 1 : 0) + (dl.h.filter_log2_bits ? 1 : 0);
+        for (uint32_t g = 0; g < dl.h.n_groups; g++) {
+            CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, (int)g, w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(),
+                               d->num_sms, w.stream));
+            w.launches++;
+        }
+        CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, sizeof(ScanCounters), cudaMemcpyDeviceToHost, w.stream));
+        CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream));
+        CU(cudaEventRecord(w.e[4], w.stream));
+    }
+    return PM_OK;
+}
+
+int finish(pm_batch *b, pm_result_view *out) {
+    pm_ctx *ctx = b->ctx;
+    // ---- phase 1: candidate/raw counts are known -> order, de-duplicate, resolve
+    for (;;) {
+        bool again = false;
+        for (auto &w : b->work) {
+            Device *d = ctx->devs[w.slot];
+            CU(cudaSetDevice(d->id));
+            CU(cudaStreamSynchronize(w.stream));
+            ScanCounters *c = w.h_ctr.as<ScanCounters>();
+            if (c->cand_overflow || c->raw_overflow) {
+                int rc;
+                if (c->cand_overflow) {
+                    w.cand_cap = std::min<uint64_t>(w.cand_cap * 8, w.total / 16 + 64);
+                    if ((rc = get(d->pool, w.cand_cap * 8, w.cand))) return rc;
+                }
+                if (c->raw_overflow) {
+                    w.raw_cap *= 8;
+                    if ((rc = get(d->pool, w.raw_cap * 8, w.raw))) return rc;
+                }
+                again = true;
+            }
+        }
+        if (!again) break;
+        int rc = scan_async(b);   // rerun with larger queues (all devices: keeps the code simple)
+        if (rc) return rc;
+    }
+    for (auto &w : b->work) {
+        Device *d = ctx->devs[w.slot];
+        CU(cudaSetDevice(d->id));
+        const DeviceLibrary &dl = b->lib->dev[w.slot];
+        ScanCounters *c = w.h_ctr.as<ScanCounters>();
+        uint64_t n_raw = c->n_raw;
+        w.n_cand = c->n_cand;
+        w.n_verified = c->n_verified;
+        int rc;
+        CU(cudaEventRecord(w.e[5], w.stream));
+        if (n_raw) {
+            size_t tb = sort_temp_bytes(n_raw);
+            if ((rc = get(d->pool, n_raw * 8, w.sorted))) return rc;
+            if ((rc = get(d->pool, n_raw * 8 + 64, w.uniq))) return rc;
+            if ((rc = get(d->pool, tb, w.temp))) return rc;
+            unsigned long long *n_unique = reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + sizeof(ScanCounters));
+            CU(launch_sort_unique(w.raw.as<unsigned long long>(), w.sorted.as<unsigned long long>(), w.uniq.as<unsigned long long>(), n_raw, n_unique,
+                                  w.temp.p, tb, w.stream));
+            w.launches += 1;
+            CU(cudaMemcpyAsync(w.h_ctr.as<char>() + sizeof(ScanCounters), n_unique, 8, cudaMemcpyDeviceToHost, w.stream));
+        } else {
+            *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + sizeof(ScanCounters)) = 0;
+        }
+        (void)dl;
+    }
+    for (auto &w : b->work) {
+        Device *d = ctx->devs[w.slot];
+        CU(cudaSetDevice(d->id));
+        CU(cudaStreamSynchronize(w.stream));
+        const DeviceLibrary &dl = b->lib->dev[w.slot];
+        w.n_events = *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + sizeof(ScanCounters));
+        int rc;
+        if (w.n_events) {
+            SoaLayout L(w.n_events);
+            if ((rc = get(d->pool, L.bytes, w.ev_soa))) return rc;
+            if ((rc = get(ctx->pinned, L.bytes, w.h_soa))) return rc;
+            CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), (int)w.pods.size(),
+                              w.uniq.as<unsigned long long>(), w.n_events, L.on(w.ev_soa.p), w.stream));
+            w.launches += 1;
+            CU(cudaEventRecord(w.e[6], w.stream));
+            CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
+        } else {
+            CU(cudaEventRecord(w.e[6], w.stream));
+        }
+        CU(cudaEventRecord(w.e[7], w.stream));
+    }
+    // ---- phase 2: gather in batch pod order
+    uint64_t total_events = 0, bytes = 0, n_cand = 0, n_ver = 0;
+    int launches = 0;
+    double ms_h2d = 0, ms_scan = 0, ms_post = 0, ms_d2h = 0;
+    for (auto &w : b->work) {
+        CU(cudaSetDevice(ctx->devs[w.slot]->id));
+        CU(cudaStreamSynchronize(w.stream));
+        total_events += w.n_events;
+        bytes += w.total;
+        n_cand += w.n_cand;
+        n_ver += w.n_verified;
+        launches += w.launches;
+        w.launches = 0;
+        float a = 0, s = 0, p1 = 0, p2 = 0, dd = 0;
+        cudaEventElapsedTime(&a, w.e[0], w.e[1]);
+        cudaEventElapsedTime(&s, w.e[2], w.e[3]);
+        cudaEventElapsedTime(&p1, w.e[3], w.e[4]);
+        cudaEventElapsedTime(&p2, w.e[5], w.e[6]);
+        cudaEventElapsedTime(&dd, w.e[6], w.e[7]);
+        ms_h2d = std::max<double>(ms_h2d, a);
+        ms_scan = std::max<double>(ms_scan, s);
+        ms_post = std::max<double>(ms_post, p1 + p2);
+        ms_d2h = std::max<double>(ms_d2h, dd);
+        w.scanned = true;
+    }
+    const size_t np = b->pods.size();
+    SoaLayout L(total_events);
+    int rc;
+    if ((rc = get(ctx->pinned, L.bytes, b->r_soa))) return rc;
+    if ((rc = get(ctx->pinned, np * 8 + (np + 1) * 8 + np * 4 + 64, b->r_pod))) return rc;
+    EventOut R = L.on(b->r_soa.p);
+    uint64_t *tags = b->r_pod.as<uint64_t>();
+    int64_t *first = reinterpret_cast<int64_t *>(tags + np);
+    int32_t *nlines = reinterpret_cast<int32_t *>(first + np + 1);
+    // per device: event ranges per local pod (events are sorted by pod on each device)
+    std::vector<std::vector<uint64_t>> dev_first(b->work.size());
+    for (size_t k = 0; k < b->work.size(); k++) {
+        DevWork &w = b->work[k];
+        dev_first[k].assign(w.pods.size() + 1, w.n_events);
+        if (w.n_events) {
+            EventOut S = SoaLayout(w.n_events).on(w.h_soa.p);
+            int prev = -1;
+            for (uint64_t i = 0; i < w.n_events; i++)
+                while (prev < S.pod[i]) dev_first[k][++prev] = i;
+            for (size_t j = (size_t)prev + 1; j <= w.pods.size(); j++) dev_first[k][j] = w.n_events;
+        }
+        dev_first[k][w.pods.size()] = w.n_events;
+    }
+    uint64_t at = 0;
+    std::vector<int> slot_index(ctx->devs.size(), -1);
+    for (size_t k = 0; k < b->work.size(); k++) slot_index[b->work[k].slot] = (int)k;
+    for (size_t i = 0; i < np; i++) {
+        const PodRef &p = b->pods[i];
+        DevWork &w = b->work[slot_index[p.dev]];
+        tags[i] = p.tag;
+        first[i] = (int64_t)at;
+        const PodDev *hp = w.h_pods.as<PodDev>();
+        int nl = hp[p.local].n_lines;
+        if (p.len == 0) nl = 1;   // "" splits into one empty line (SPEC.md section 2)
+        nlines[i] = nl;
+        uint64_t a = dev_first[slot_index[p.dev]][p.local], e = dev_first[slot_index[p.dev]][p.local + 1];
+        if (e > a) {
+            EventOut S = SoaLayout(w.n_events).on(w.h_soa.p);
+            size_t cnt = e - a;
+            memcpy(R.line_start + at, S.line_start + a, cnt * 8);
+            memcpy(R.ctx_start + at, S.ctx_start + a, cnt * 8);
+            memcpy(R.ctx_end + at, S.ctx_end + a, cnt * 8);
+            memcpy(R.score + at, S.score + a, cnt * 8);
+            memcpy(R.pattern + at, S.pattern + a, cnt * 4);
+            memcpy(R.line_no + at, S.line_no + a, cnt * 4);
+            memcpy(R.line_len + at, S.line_len + a, cnt * 4);
+            memcpy(R.ctx_first + at, S.ctx_first + a, cnt * 4);
+            memcpy(R.ctx_last + at, S.ctx_last + a, cnt * 4);
+            for (size_t j = 0; j < cnt; j++) R.pod[at + j] = (int32_t)i;
+            at += cnt;
+        }
+    }
+    first[np] = (int64_t)at;
+    pm_result_view &v = b->view;
+    memset(&v, 0, sizeof v);
+    v.n_events = (int64_t)total_events;
+    v.n_pods = (int64_t)np;
+    v.pod_index = R.pod;
+    v.pattern_index = R.pattern;
+    v.line_no = R.line_no;
+    v.line_start = R.line_start;
+    v.line_len = R.line_len;
+    v.ctx_first_line = R.ctx_first;
+    v.ctx_last_line = R.ctx_last;
+    v.ctx_start = R.ctx_start;
+    v.ctx_end = R.ctx_end;
+    v.score = R.score;
+    v.pod_tag = tags;
+    v.pod_first_event = first;
+    v.pod_n_lines = nlines;
+    v.ms_h2d = ms_h2d;
+    v.ms_scan = ms_scan;
+    v.ms_post = ms_post;
+    v.ms_d2h = ms_d2h;
+    v.bytes_scanned = (int64_t)bytes;
+    v.n_candidates = (int64_t)n_cand;
+    v.n_verified = (int64_t)n_ver;
+    v.gpu_launches = launches;
+    if (out) *out = v;
+    return PM_OK;
+}
+
+}  // namespace
+
+// ============================================================================ C ABI
+extern "C" {
+
+int pm_abi_version(void) { return PM_ABI_VERSION; }
+
+const char *pm_last_error(void) { return g_err.c_str(); }
+
+int pm_init(int n_devices, pm_ctx **out) {
+    if (!out) return fail(PM_E_INVALID, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return fail(PM_E_NO_DEVICE, "no CUDA device (%s); this engine has no CPU path", e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+    }
+    if (n_devices <= 0 || n_devices > count) n_devices = count;
+    pm_ctx *ctx = new pm_ctx();
+    ctx->pinned.pinned = true;
+    for (int i = 0; i < n_devices; i++) {
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, i) != cudaSuccess || prop.major < 10) {
+            for (auto *d : ctx->devs) delete d;
+            delete ctx;
+            return fail(PM_E_NO_DEVICE, "device %d is not sm_100-class: the kernels are built for sm_100a only", i);
+        }
+        Device *d = new Device();
+        d->id = i;
+        d->num_sms = prop.multiProcessorCount;
+        d->pool.device = i;
+        ctx->devs.push_back(d);
+    }
+    *out = ctx;
+    return PM_OK;
+}
+
+void pm_shutdown(pm_ctx *ctx) {
+    if (!ctx) return;
+    if (ctx->current) lib_unref(ctx->current);
+    for (auto *d : ctx->devs) {
+        cudaSetDevice(d->id);
+        cudaDeviceSynchronize();
+        d->pool.trim();
+        delete d;
+    }
+    ctx->pinned.trim();
+    for (auto &kv : ctx->user_pinned) cudaFreeHost(kv.first);
+    delete ctx;
+}
+
+int pm_device_count(const pm_ctx *ctx) { return ctx ? (int)ctx->devs.size() : 0; }
+
+int pm_library_compile(pm_ctx *ctx, const uint8_t *spec, size_t n, pm_library **out, pm_compile_report *rep) {
+    pm_compile_report local;
+    if (!rep) rep = &local;
+    if (!out || !spec) return fail(PM_E_INVALID, "null argument");
+    *out = nullptr;
+    pm_library *l = new pm_library();
+    l->owner = ctx;
+    int rc = compile_library(reinterpret_cast<const char *>(spec), n, l->lib, *rep);
+    if (rc != PM_OK) {
+        delete l;
+        return fail(rc, "pattern %d (%s): %s%s", rep->pattern_index, rep->pattern_id, rep->message,
+                    rep->secondary_index >= 0 ? " [secondary pattern]" : "");
+    }
+    if (l->lib.patterns.size() >= (1u << kPatternBits)) {
+        delete l;
+        return fail(PM_E_TOO_COMPLEX, "more than %u patterns", 1u << kPatternBits);
+    }
+    *out = l;
+    return PM_OK;
+}
+
+int pm_library_publish(pm_ctx *ctx, pm_library *l) {
+    if (!ctx || !l) return fail(PM_E_INVALID, "null argument");
+    if (l->dev.empty()) {
+        l->owner = ctx;
+        l->dev.resize(ctx->devs.size());
+        l->dev_blobs.assign(ctx->devs.size(), nullptr);
+        for (size_t d = 0; d < ctx->devs.size(); d++) {
+            CU(cudaSetDevice(ctx->devs[d]->id));
+            CU(cudaMalloc(&l->dev_blobs[d], l->lib.blob.size()));
+            CU(cudaMemcpy(l->dev_blobs[d], l->lib.blob.data(), l->lib.blob.size(), cudaMemcpyHostToDevice));
+            l->dev[d].blob = reinterpret_cast<const uint8_t *>(l->dev_blobs[d]);
+            l->dev[d].h = *l->lib.header();
+        }
+    }
+    pm_library *old;
+    {
+        std::lock_guard<std::mutex> g(ctx->mu);
+        old = ctx->current;
+        l->refs.fetch_add(1);
+        ctx->current = l;
+    }
+    lib_unref(old);
+    return PM_OK;
+}
+
+void pm_library_free(pm_library *l) { lib_unref(l); }
+
+int pm_library_pattern_count(const pm_library *l) { return l ? (int)l->lib.patterns.size() : 0; }
+
+const char *pm_library_pattern_meta_json(const pm_library *l, int i) {
+    if (!l || i < 0 || i >= (int)l->lib.patterns.size()) return nullptr;
+    return l->lib.patterns[i].meta_json.c_str();
+}
+
+void *pm_host_alloc(pm_ctx *ctx, size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        fail(PM_E_NOMEM, "cudaHostAlloc(%zu) failed", bytes);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> g(ctx->user_pinned_mu);
+    ctx->user_pinned[p] = bytes;
+    return p;
+}
+
+void pm_host_free(pm_ctx *ctx, void *p) {
+    if (!p) return;
+    std::lock_guard<std::mutex> g(ctx->user_pinned_mu);
+    if (ctx->user_pinned.erase(p)) cudaFreeHost(p);
+}
+
+int pm_batch_begin(pm_ctx *ctx, pm_batch **out) {
+    if (!ctx || !out) return fail(PM_E_INVALID, "null argument");
+    pm_batch *b = new pm_batch();
+    b->ctx = ctx;
+    memset(&b->view, 0, sizeof b->view);
+    *out = b;
+    return PM_OK;
+}
+
+int pm_batch_add_pod(pm_batch *b, const uint8_t *log, size_t n, uint64_t tag) {
+    if (!b || (!log && n)) return fail(PM_E_INVALID, "null argument");
+    if (b->staged) return fail(PM_E_INVALID, "batch already staged");
+    PodRef p;
+    p.ptr = log;
+    p.len = n;
+    p.eff_len = effective_len(log, n);
+    p.tag = tag;
+    b->pods.push_back(p);
+    return PM_OK;
+}
+
+int pm_batch_stage(pm_batch *b) {
+    if (!b) return fail(PM_E_INVALID, "null argument");
+    int rc = stage(b);
+    if (rc) return rc;
+    for (auto &w : b->work) {
+        CU(cudaSetDevice(b->ctx->devs[w.slot]->id));
+        CU(cudaStreamSynchronize(w.stream));
+    }
+    return PM_OK;
+}
+
+int pm_batch_submit(pm_batch *b) {
+    if (!b) return fail(PM_E_INVALID, "null argument");
+    int rc = stage(b);
+    if (rc) return rc;
+    rc = scan_async(b);
+    if (rc) return rc;
+    b->submitted = true;
+    return PM_OK;
+}
+
+int pm_batch_wait(pm_batch *b, pm_result_view *out) {
+    if (!b || !b->submitted) return fail(PM_E_INVALID, "batch was not submitted");
+    b->submitted = false;
+    return finish(b, out);
+}
+
+int pm_batch_rescan(pm_batch *b, pm_result_view *out) {
+    if (!b || !b->staged) return fail(PM_E_INVALID, "batch is not staged");
+    int rc = scan_async(b);
+    if (rc) return rc;
+    return finish(b, out);
+}
+
+void pm_batch_release(pm_batch *b) {
+    if (!b) return;
+    release_work(b);
+    put(b->ctx->pinned, b->r_soa);
+    put(b->ctx->pinned, b->r_pod);
+    lib_unref(b->lib);
+    delete b;
+}
+
+int64_t pm_batch_line_index(pm_batch *b, int pod, int64_t *out, int64_t cap) {
+    if (!b || pod < 0 || pod >= (int)b->pods.size()) return fail(PM_E_INVALID, "bad pod index");
+    const PodRef &p = b->pods[pod];
+    DevWork *w = nullptr;
+    for (auto &x : b->work)
+        if (x.slot == p.dev) w = &x;
+    if (!w || !w->scanned) return fail(PM_E_INVALID, "batch has not been scanned");
+    Device *d = b->ctx->devs[w->slot];
+    CU(cudaSetDevice(d->id));
+    const PodDev *hp = w->h_pods.as<PodDev>();
+    int n_lines = hp[p.local].n_lines;
+    if (p.len == 0) {
+        if (cap >= 1 && out) out[0] = 0;
+        return 1;
+    }
+    if (n_lines == 0) return 0;
+    if (!out || cap < n_lines) return fail(PM_E_INVALID, "line table needs %d entries", n_lines);
+    int rc;
+    if ((rc = get(d->pool, (size_t)n_lines * 8, w->lines_tmp))) return rc;
+    CU(launch_line_starts(w->text.as<uint8_t>(), w->tile_prefix.as<unsigned long long>(), hp[p.local].nl_before, n_lines, hp[p.local].start,
+                          hp[p.local].eff_end, w->lines_tmp.as<long long>(), d->num_sms, w->stream));
+    CU(cudaMemcpyAsync(out, w->lines_tmp.p, (size_t)n_lines * 8, cudaMemcpyDeviceToHost, w->stream));
+    CU(cudaStreamSynchronize(w->stream));
+    return n_lines;
+}
+
+}  // extern "C"
+
+// Accessors for pm_service.cc (same shared object, not part of the C ABI)
+namespace pm {
+std::string &ctx_response_buffer(pm_ctx *ctx) { return ctx->parse_response; }
+pm_library *ctx_current_library(pm_ctx *ctx) {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    return ctx->current;
+}
+const CompiledLibrary &library_compiled(const pm_library *l) { return l->lib; }
+}  // namespace pm
