@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""Benchmark of the log-scan hot path (BASELINE.json metric: log-scan GB/s, % of HBM roofline).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the CPU loop on host cores
+
+A step is one pass of the scan over one batch: the synthetic 1 GiB crash-log corpus of BASELINE
+config 2 against the 500-pattern synthetic library, per GPU (pods shard over ranks with no
+collective, so N ranks scan N corpora: weak scaling).  One JSON line is printed by rank 0.
+
+  value      corpus bytes / device time of a step with the corpus already resident in HBM
+             (one CUDA-event pair from the first kernel to the last result copy; max over ranks)
+  e2e        the same metric through the public C ABI with HOST buffers: begin/add_pod/submit/
+             wait/release per step, H2D of the log and D2H of the results inside the timed region
+  roofline   k_scan alone: corpus bytes / its CUDA-event duration against the measured HBM peak
+  cpu_baseline  the reference-style loop (per line x per pattern regex search) on host cores over
+             a bounded sample, timed beside it (N=1 only)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CORPUS_BYTES = 1 << 30
+N_PATTERNS = 500
+P_HIT = 1e-3
+CPU_SAMPLE_BYTES = 64 << 20
+REF_STEP_BYTES = 16 << 20
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--corpus-bytes", type=int, default=CORPUS_BYTES)
+    ap.add_argument("--patterns", type=int, default=N_PATTERNS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index: str):
+        self.samples = []
+        self.proc = None
+        self.gpu = gpu_index
+        self.marks = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", self.gpu, "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def mark(self):
+        self.marks.append(time.time())
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+
+    def summary(self):
+        rows = []
+        lo = self.marks[0] if self.marks else 0
+        hi = self.marks[-1] if len(self.marks) > 1 else 1e18
+        for t, line in self.samples:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                rows.append((t, float(parts[0]), float(parts[1]), parts[3:7]))
+            except ValueError:
+                continue
+        sel = [r for r in rows if lo - 0.05 <= r[0] <= hi + 0.05] or rows
+        if not sel:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        mhz = sorted(r[1] for r in sel)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in sel for i in range(4) if r[3][i].lower().startswith("active")})
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": sel[0][2], "reasons": reasons, "samples": len(sel)}
+
+
+def peak_hbm():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_scan(corpus, lib_json, nbytes, threads):
+    """The reference-style CPU loop on `nbytes` of the corpus; returns (seconds, bytes, matches)."""
+    import numpy as np
+    from oracle import pcre2_oracle as po
+    sample = corpus[:nbytes]
+    cut = int(np.flatnonzero(sample == 10)[-1]) + 1
+    sample = sample[:cut]
+    lib = po.Pcre2Library([p["primary_pattern"]["regex"] for p in lib_json["patterns"]])
+    t0 = time.perf_counter()
+    starts, lens = po.split(sample)
+    _, _, total = po.scan(lib, sample, starts, lens, threads=threads)
+    dt = time.perf_counter() - t0
+    lib.close()
+    return dt, cut, total
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU shape for this path (split lines, per line x per
+    pattern unanchored regex search) on all host cores.  The JVM engine (java.util.regex) is not in
+    this image; PCRE2-JIT stands in (oracle/scan_pcre2.c) -- kind "port"."""
+    if rank != 0:
+        return
+    import numpy as np
+    from operator_b200 import synth
+    lib_json, wit, swit = synth.make_library(args.patterns)
+    step_bytes = min(REF_STEP_BYTES, args.corpus_bytes)
+    corpus, _ = synth.make_corpus(step_bytes, wit, swit, p_hit=P_HIT)
+    cores = os.cpu_count() or 1
+    for _ in range(min(args.warmup, 1)):
+        cpu_scan(corpus, lib_json, min(step_bytes, 2 << 20), cores)
+    t_total, b_total = 0.0, 0
+    steps = max(1, min(args.steps, 5))
+    for _ in range(steps):
+        dt, nb, _ = cpu_scan(corpus, lib_json, step_bytes, cores)
+        t_total += dt
+        b_total += nb
+    gbs = b_total / t_total / 1e9
+    sample = "%d steps x first %d MiB of the config-2 corpus, %d patterns, PCRE2-JIT, %d threads" % (steps, step_bytes >> 20, args.patterns, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": "log_scan_throughput", "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * t_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1]: 1 GiB synthetic crash-log corpus vs 500-pattern library (bounded sample per step)",
+                   "patterns": args.patterns, "p_hit": P_HIT, "sample_bytes_per_step": step_bytes},
+        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    from operator_b200 import Engine, dist, synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: the scan has no CPU path (use --impl reference for the CPU loop)")
+    torch.cuda.set_device(local)
+    dev = "cuda:%d" % local
+    if world > 1:
+        dist.init("nccl")
+
+    # ---- inputs: library + this rank's corpus in pinned host memory (a1: the ingest side)
+    lib_json, wit, swit = synth.make_library(args.patterns)
+    # one context per process, on this rank's GPU
+    visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+    gpu_index = visible.split(",")[local] if visible else str(local)
+    eng = Engine(devices=[local])
+    eng.compile_library(lib_json).publish()
+    pinned = eng.pinned(args.corpus_bytes)
+    corpus, n_lines = synth.make_corpus(args.corpus_bytes, wit, swit, p_hit=P_HIT, first_line=rank << 36, out=pinned.array)
+    nbytes = int(corpus.size)
+
+    sampler = ClockSampler(gpu_index)
+    sampler.start()
+
+    def sync_all():
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    # ---- leg 1: device-resident corpus (value + roofline)
+    b = eng.batch()
+    b.add_pod(corpus, rank)
+    b.stage()
+    for _ in range(max(args.warmup, 3)):
+        r = b.rescan(copy=False)
+    sync_all()
+    sampler.mark()
+    t0 = time.perf_counter()
+    ms_total = ms_scan = ms_post = 0.0
+    launches = 0
+    for _ in range(args.steps):
+        r = b.rescan(copy=False)
+        ms_total += r.ms_total
+        ms_scan += r.ms_scan
+        ms_post += r.ms_post
+        launches += r.gpu_launches
+    sync_all()
+    wall_dev = time.perf_counter() - t0
+    n_events, n_cand = r.n_events, r.n_candidates
+    d2h_bytes = int(r.n_events) * 64 + 64
+    b.release()
+
+    # ---- leg 2: end to end through the C ABI with host buffers
+    for _ in range(max(min(args.warmup, 3), 1)):
+        eng.scan([corpus])
+    sync_all()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 20))
+    ms_h2d = 0.0
+    for _ in range(e2e_steps):
+        bb = eng.batch()
+        bb.add_pod(corpus, rank)
+        bb.submit()
+        rr = bb.wait(copy=False)
+        ms_h2d += rr.ms_h2d
+        bb.release()
+    sync_all()
+    wall_e2e = time.perf_counter() - t0
+    sampler.mark()
+    sampler.stop()
+
+    # ---- reductions: max time over ranks, sum of bytes
+    step_ms = dist.max_over_ranks(ms_total / args.steps, dev)
+    scan_ms = dist.max_over_ranks(ms_scan / args.steps, dev)
+    e2e_s = dist.max_over_ranks(wall_e2e / e2e_steps, dev)
+    wall_dev_s = dist.max_over_ranks(wall_dev / args.steps, dev)
+    total_bytes = dist.sum_over_ranks(nbytes, dev)
+    h2d_ms = dist.max_over_ranks(ms_h2d / e2e_steps, dev)
+
+    if rank == 0:
+        peak, peak_src = peak_hbm()
+        achieved = nbytes / (scan_ms * 1e-3) / 1e9          # per GPU: the kernel's own launch
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "k_scan_traffic.json")) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        out = {
+            "metric": "log_scan_throughput", "value": total_bytes / (step_ms * 1e-3) / 1e9, "unit": "GB/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[1]: 1 GiB synthetic crash-log corpus vs 500-pattern library, per GPU", "corpus_bytes_per_gpu": nbytes,
+                       "lines_per_gpu": n_lines, "patterns": args.patterns, "p_hit": P_HIT, "parallelism": "pod-sharded x%d, no collective" % world,
+                       "l2": "input (1 GiB per GPU) is larger than the 126 MB L2; no flush between iterations",
+                       "events_per_step": int(n_events), "filter_candidates_per_step": int(n_cand)},
+            "e2e": {"value": total_bytes / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": nbytes + 64, "d2h_bytes_per_step": d2h_bytes,
+                    "h2d_ms_per_step": h2d_ms, "h2d_gbs": nbytes / (h2d_ms * 1e-3) / 1e9 if h2d_ms else None, "steps": e2e_steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_scan", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "frac_of_nominal_8TBs": achieved / 8000.0, "peak_source": peak_src, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": nbytes, "avg_launch_ms": scan_ms,
+                         "whole_step_frac": (nbytes / (step_ms * 1e-3) / 1e9) / peak},
+            "timing": {"device_ms_per_step": step_ms, "k_scan_ms": scan_ms, "post_ms": ms_post / args.steps, "host_wall_ms_per_step": wall_dev_s * 1e3},
+            "clocks": sampler.summary(),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            dt, nb, _ = cpu_scan(corpus, lib_json, min(CPU_SAMPLE_BYTES, nbytes), cores)
+            out["cpu_baseline"] = {"value": nb / dt / 1e9, "unit": "GB/s", "cores": cores, "kind": "port",
+                                   "sample": "first %d MiB of the same corpus, all %d patterns, per line x per pattern PCRE2-JIT search "
+                                             "(JVM unavailable on this box), %d threads, %.1f s" % (nb >> 20, args.patterns, cores, dt)}
+        print(json.dumps(out))
+    pinned.free()
+    eng.close()
+    if world > 1:
+        import torch.distributed as td
+        td.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -90,6 +90,9 @@ typedef struct pm_result_view {
     /* timings of the last run, milliseconds, measured with CUDA events on the batch's streams
      * (max over devices) */
     double ms_h2d, ms_scan, ms_post, ms_d2h;
+    /* first kernel of the scan to the last result copy, one CUDA-event pair per device (includes
+     * the host round trip that sizes the sort), max over devices */
+    double ms_total;
     /* counters */
     int64_t bytes_scanned, n_candidates, n_verified, gpu_launches;
 } pm_result_view;
@@ -98,6 +101,8 @@ typedef struct pm_result_view {
 int pm_abi_version(void);
 /* n_devices <= 0: use every visible device. */
 int pm_init(int n_devices, pm_ctx **out);
+/* Explicit device ordinals (one process per GPU: pass the rank's local device). */
+int pm_init_devices(const int *device_ids, int n, pm_ctx **out);
 void pm_shutdown(pm_ctx *);
 const char *pm_last_error(void);
 int pm_device_count(const pm_ctx *);

@@ -77,7 +77,8 @@ struct GroupDesc {
     uint16_t nstates, stride, first_accept, pad;
 };
 
-PM_HD uint32_t gram_filter_bit(uint32_t gram, uint32_t log2_bits) { return (gram * 0x9E3779B1u) >> (32u - log2_bits); }
+constexpr uint32_t kFilterMult0 = 0x9E3779B1u;   // default multiplier; the runtime may reseed (pm_runtime.cu)
+PM_HD uint32_t gram_filter_bit(uint32_t gram, uint32_t log2_bits, uint32_t mult = kFilterMult0) { return (gram * mult) >> (32u - log2_bits); }
 PM_HD uint32_t gram_table_slot(uint32_t gram, uint32_t log2_cap) { return (gram * 0x85EBCA6Bu) >> (32u - log2_cap); }
 
 }  // namespace pm

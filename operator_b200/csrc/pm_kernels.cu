@@ -52,16 +52,16 @@ __device__ __forceinline__ unsigned lanemask_lt() {
 
 // ------------------------------------------------------------------------------------ k_scan
 template <int BITS, bool FOLD>
-__device__ __forceinline__ uint32_t filter_word(uint32_t w, const uint32_t *bm) {
+__device__ __forceinline__ uint32_t filter_word(uint32_t w, const uint32_t *bm, uint32_t mult) {
     uint32_t g = FOLD ? (w | 0x20202020u) : w;
-    uint32_t bit = (g * 0x9E3779B1u) >> (32 - BITS);
+    uint32_t bit = (g * mult) >> (32 - BITS);
     return (bm[bit >> 5] >> (bit & 31u)) & 1u;
 }
 
 template <int BITS, bool FOLD>
 __global__ void __launch_bounds__(kScanThreads, 1)
 k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g,
-       uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+       uint32_t mult, uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
        ScanCounters *__restrict__ ctr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int kBitmapWords = (1 << BITS) / 32;
@@ -89,8 +89,8 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
             uint32_t f0 = not_newline_flags(v[j].x), f1 = not_newline_flags(v[j].y);
             uint32_t f2 = not_newline_flags(v[j].z), f3 = not_newline_flags(v[j].w);
             nz += __popc(f0 | (f1 >> 1) | (f2 >> 2) | (f3 >> 3));
-            uint32_t m4 = filter_word<BITS, FOLD>(v[j].x, bm) | (filter_word<BITS, FOLD>(v[j].y, bm) << 1) |
-                          (filter_word<BITS, FOLD>(v[j].z, bm) << 2) | (filter_word<BITS, FOLD>(v[j].w, bm) << 3);
+            uint32_t m4 = filter_word<BITS, FOLD>(v[j].x, bm, mult) | (filter_word<BITS, FOLD>(v[j].y, bm, mult) << 1) |
+                          (filter_word<BITS, FOLD>(v[j].z, bm, mult) << 2) | (filter_word<BITS, FOLD>(v[j].w, bm, mult) << 3);
             unsigned b = __ballot_sync(FULL, m4 != 0);
             if (b) {   // warp-uniform, rare: stage (group, mask) entries, flush 32 at a time
                 if (m4) wq[qn + __popc(b & lt)] = ((t * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
@@ -266,12 +266,29 @@ __device__ bool line_matches(const uint8_t *text, unsigned long long a, unsigned
     return s == t.accept;
 }
 
+// Is `le` (the position of a '\n') the first padding byte after some pod, i.e. not a separator
+// that belongs to the log?  Only called when the batch has a pod ending in a lone '\r'.
+__device__ bool is_pod_raw_end(const PodTable &pt, unsigned long long le) {
+    int lo = 0, hi = pt.n - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (pt.pods[mid].start <= le) lo = mid; else hi = mid - 1;
+    }
+    return pt.n > 0 && pt.pods[lo].raw_end == le;
+}
+
+// End of the line whose '\n' sits at `le`: the '\r' of a "\r\n" separator is not part of the line.
+__device__ __forceinline__ unsigned long long strip_cr(const uint8_t *text, const PodTable &pt, unsigned long long ls, unsigned long long le) {
+    if (le > ls && text[le - 1] == '\r' && !(pt.any_trailing_cr && is_pod_raw_end(pt, le))) return le - 1;
+    return le;
+}
+
 // ------------------------------------------------------------------------------------ k_pad / k_pods
-__global__ void k_pad(uint8_t *text, const PodDev *pods, const unsigned long long *raw_end, int n_pods, unsigned long long total) {
+__global__ void k_pad(uint8_t *text, const PodDev *pods, int n_pods, unsigned long long total) {
     int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (w > n_pods) return;
     // gap w: [raw_end[w-1], start[w]) ; gap 0 is the header, gap n_pods runs to the end of the buffer
-    unsigned long long a = w == 0 ? 0 : raw_end[w - 1], b = w == n_pods ? total : pods[w].start;
+    unsigned long long a = w == 0 ? 0 : pods[w - 1].raw_end, b = w == n_pods ? total : pods[w].start;
     for (unsigned long long p = a + lane; p < b; p += 32) text[p] = '\n';
 }
 
@@ -289,9 +306,10 @@ __global__ void k_pods(const uint8_t *text, const unsigned long long *tile_prefi
 
 // ------------------------------------------------------------------------------------ k_confirm
 __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h,
-                                                 const unsigned long long *__restrict__ cand, unsigned long long *__restrict__ raw, unsigned long long raw_cap,
-                                                 ScanCounters *ctr) {
-    const unsigned long long n = ctr->n_cand;
+                                                 PodTable pt, const unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+                                                 unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
+    if (ctr->cand_overflow) return;   // the host reruns the scan with a larger queue
+    const unsigned long long n = ctr->n_cand < cand_cap ? ctr->n_cand : cand_cap;
     const uint32_t *gk = reinterpret_cast<const uint32_t *>(blob + h.off_gram_keys);
     const uint32_t *gf = reinterpret_cast<const uint32_t *>(blob + h.off_gram_first);
     const uint32_t *gc = reinterpret_cast<const uint32_t *>(blob + h.off_gram_count);
@@ -331,7 +349,7 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
                 unsigned long long ls = p, le = p;
                 while (text[ls - 1] != '\n') ls--;
                 while (text[le] != '\n') le++;
-                unsigned long long lend = (le > ls && text[le - 1] == '\r') ? le - 1 : le;
+                unsigned long long lend = strip_cr(text, pt, ls, le);
                 UnitTables ut = unit_tables(blob, h, pd[pr.pattern].unit);
                 if (line_matches(text, ls, lend, ut)) {
                     unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
@@ -353,7 +371,7 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
 // above is the one built for bandwidth.
 constexpr int kDfaThreads = 256, kDfaChunk = 256;
 
-__global__ void __launch_bounds__(kDfaThreads) k_dfa_scan(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h, int group,
+__global__ void __launch_bounds__(kDfaThreads) k_dfa_scan(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h, PodTable pt, int group,
                                                           unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const GroupDesc gd = reinterpret_cast<const GroupDesc *>(blob + h.off_groups)[group];
@@ -381,7 +399,7 @@ __global__ void __launch_bounds__(kDfaThreads) k_dfa_scan(const uint8_t *__restr
             for (;;) {
                 uint8_t b = text[p];
                 // a line ends at '\n', or at the '\r' of a "\r\n" separator (SPEC.md section 2)
-                bool crlf = (b == '\r') && text[p + 1] == '\n';
+                bool crlf = (b == '\r') && text[p + 1] == '\n' && !(pt.any_trailing_cr && is_pod_raw_end(pt, p + 1));
                 bool eol = (b == '\n') || crlf;
                 if (crlf) p++;
                 s = tab[s * stride + (eol ? stride - 1 : cmap[b])];
@@ -480,8 +498,10 @@ __device__ void warp_collect_backward(const uint8_t *text, unsigned long long be
 }
 
 __global__ void __launch_bounds__(kResolveWarps * 32) k_resolve(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
-                                                                const unsigned long long *__restrict__ tile_prefix, const PodDev *__restrict__ pods, int n_pods,
+                                                                const unsigned long long *__restrict__ tile_prefix, PodTable pt,
                                                                 const unsigned long long *__restrict__ uniq, unsigned long long n_events, EventOut out) {
+    const PodDev *pods = pt.pods;
+    const int n_pods = pt.n;
     __shared__ unsigned long long fwd_s[kResolveWarps][kCtxSlots];   // fwd[i]: '\n' that ends line L+i
     __shared__ unsigned long long bwd_s[kResolveWarps][kCtxSlots];   // bwd[i]: '\n' that precedes line L-i
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -524,7 +544,7 @@ __global__ void __launch_bounds__(kResolveWarps * 32) k_resolve(const uint8_t *_
                 a = bwd[-rel] + 1;
                 b = bwd[-rel - 1];
             }
-            if (b > a && text[b - 1] == '\r') b--;
+            if (b > a && text[b - 1] == '\r' && !(pt.any_trailing_cr && b == pod.raw_end)) b--;
         };
 
         // ---- context (a13)
@@ -640,27 +660,27 @@ __global__ void __launch_bounds__(256) k_line_starts(const uint8_t *__restrict__
 }
 
 template <int BITS>
-cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, uint32_t *tile_nl, unsigned long long *cand,
+cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, uint32_t mult, uint32_t *tile_nl, unsigned long long *cand,
                              unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
     size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
     cudaError_t e;
     if (fold) {
         e = cudaFuncSetAttribute(k_scan<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr);
     } else {
         e = cudaFuncSetAttribute(k_scan<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr);
     }
     return cudaGetLastError();
 }
 
 }  // namespace
 
-cudaError_t launch_pad(uint8_t *text, const PodDev *pods, const unsigned long long *pod_raw_end, int n_pods, unsigned long long total_bytes, cudaStream_t s) {
+cudaError_t launch_pad(uint8_t *text, const PodDev *pods, int n_pods, unsigned long long total_bytes, cudaStream_t s) {
     int warps = n_pods + 1, threads = 128, blocks = (warps * 32 + threads - 1) / threads;
-    k_pad<<<blocks, threads, 0, s>>>(text, pods, pod_raw_end, n_pods, total_bytes);
+    k_pad<<<blocks, threads, 0, s>>>(text, pods, n_pods, total_bytes);
     return cudaGetLastError();
 }
 
@@ -671,14 +691,15 @@ cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const D
         k_scan_nl_only<<<num_sms, kScanThreads, 0, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, tile_nl);
         return cudaGetLastError();
     }
-    const uint4 *bitmap = reinterpret_cast<const uint4 *>(lib.blob + h.off_bitmap);
+    const uint4 *bitmap = reinterpret_cast<const uint4 *>(lib.bitmap);
+    const uint32_t mult = lib.mult;
     switch (h.filter_log2_bits) {
-        case 15: return launch_scan_bits<15>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 16: return launch_scan_bits<16>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 17: return launch_scan_bits<17>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 18: return launch_scan_bits<18>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 19: return launch_scan_bits<19>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 20: return launch_scan_bits<20>(h.filter_fold, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 15: return launch_scan_bits<15>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 16: return launch_scan_bits<16>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 17: return launch_scan_bits<17>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 18: return launch_scan_bits<18>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 19: return launch_scan_bits<19>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 20: return launch_scan_bits<20>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
         default: return cudaErrorInvalidValue;
     }
 }
@@ -699,20 +720,20 @@ cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_pref
     return cudaGetLastError();
 }
 
-cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, const unsigned long long *cand, unsigned long long *raw,
-                           unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, const unsigned long long *cand,
+                           unsigned long long cand_cap, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
     if (lib.h.filter_log2_bits == 0) return cudaSuccess;
-    k_confirm<<<num_sms * 4, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, cand, raw, raw_cap, ctr);
+    k_confirm<<<num_sms * 4, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, pt, cand, cand_cap, raw, raw_cap, ctr);
     return cudaGetLastError();
 }
 
-cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, int group, unsigned long long *raw,
+cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group, unsigned long long *raw,
                             unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
     // host copy of the group's size is not kept: budget the shared memory for the compiler's limit
     size_t smem = 256 + 96 * 1024;
     cudaError_t e = cudaFuncSetAttribute(k_dfa_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    k_dfa_scan<<<num_sms * 2, kDfaThreads, smem, s>>>(text, total_bytes, lib.blob, lib.h, group, raw, raw_cap, ctr);
+    k_dfa_scan<<<num_sms * 2, kDfaThreads, smem, s>>>(text, total_bytes, lib.blob, lib.h, pt, group, raw, raw_cap, ctr);
     return cudaGetLastError();
 }
 
@@ -739,12 +760,12 @@ cudaError_t launch_sort_unique(unsigned long long *raw, unsigned long long *sort
     return cub::DeviceSelect::Flagged(cub_temp, cub_bytes, sorted, flags, uniq, n_unique, (long long)n, s);
 }
 
-cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, const PodDev *pods, int n_pods,
+cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
                            const unsigned long long *uniq, unsigned long long n_events, EventOut out, cudaStream_t s) {
     if (n_events == 0) return cudaSuccess;
     unsigned blocks = (unsigned)((n_events + kResolveWarps - 1) / kResolveWarps);
     if (blocks > 148u * 16u) blocks = 148u * 16u;
-    k_resolve<<<blocks, kResolveWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pods, n_pods, uniq, n_events, out);
+    k_resolve<<<blocks, kResolveWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events, out);
     return cudaGetLastError();
 }
 

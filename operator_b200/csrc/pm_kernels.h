@@ -3,8 +3,8 @@
 //
 // Device data layout of one staged batch (see DESIGN.md "Data layout in HBM"):
 //   text        [16 x '\n'] pod0 bytes, '\n' padding to the next 16-byte boundary (>= 1 byte),
-//               pod1 ..., '\n' padding up to a multiple of kTileBytes.  Every line of every
-//               pod is therefore delimited by '\n' on both sides inside the buffer.
+//               pod1 ..., '\n' padding up to a multiple of kTileBytes, one more tile of '\n'.
+//               Every line of every pod is therefore delimited by '\n' on both sides.
 //   tile_nl     u32 per 2 KiB tile: number of '\n' bytes in the tile          (k_scan)
 //   tile_prefix u64 per tile: '\n' bytes before the tile                      (k_prefix_*)
 //   cand        u64 per filter hit: (16-byte group index << 4) | word mask    (k_scan)
@@ -25,7 +25,9 @@ constexpr int kMaxCtxLines = 1000;      // lines_before / lines_after / proximit
 
 struct DeviceLibrary {
     const uint8_t *blob = nullptr;      // device copy of the compiled blob
-    BlobHeader h;                       // host copy of its header
+    const uint8_t *bitmap = nullptr;    // device gram filter in use (inside the blob, or a reseeded copy)
+    uint32_t mult = 0;                  // odd multiplier the bitmap was built with
+    BlobHeader h;                       // host copy of the blob header
 };
 
 struct ScanCounters {                   // device-resident, zeroed before every scan
@@ -39,9 +41,19 @@ struct ScanCounters {                   // device-resident, zeroed before every 
 struct PodDev {                         // per pod, device-resident
     unsigned long long start;           // offset of the pod's first byte in `text`
     unsigned long long eff_end;         // start + length without trailing separators (SPEC.md s.2)
+    unsigned long long raw_end;         // start + length
     unsigned long long nl_before;       // '\n' bytes in text[0, start)            (k_pods)
     int n_lines;                        // lines of the pod (0 when eff_end == start)
     int pad;
+};
+
+// Pod table as the kernels see it.  any_trailing_cr: some pod ends in a lone '\r'; only then
+// can a '\r' in front of the '\n' padding be mistaken for the '\r' of a "\r\n" separator, and
+// only then do the kernels pay for a pod lookup when they strip it.
+struct PodTable {
+    const PodDev *pods;
+    int n;
+    int any_trailing_cr;
 };
 
 struct EventOut {                       // SoA result rows, device pointers
@@ -50,27 +62,25 @@ struct EventOut {                       // SoA result rows, device pointers
     double *score;
 };
 
-cudaError_t launch_pad(uint8_t *text, const PodDev *pods, const unsigned long long *pod_raw_end, int n_pods,
-                       unsigned long long total_bytes, cudaStream_t s);
+cudaError_t launch_pad(uint8_t *text, const PodDev *pods, int n_pods, unsigned long long total_bytes, cudaStream_t s);
 cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const DeviceLibrary &lib, uint32_t *tile_nl,
                         unsigned long long *cand, unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
 // Exclusive prefix over tile_nl -> tile_prefix.  `scratch` holds ceil(n_tiles / 4096) + 1 u64.
 cudaError_t launch_prefix(const uint32_t *tile_nl, unsigned long long *tile_prefix, unsigned long long n_tiles,
                           unsigned long long *scratch, cudaStream_t s);
 cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_prefix, PodDev *pods, int n_pods, cudaStream_t s);
-cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib,
-                           const unsigned long long *cand, unsigned long long *raw, unsigned long long raw_cap,
-                           ScanCounters *ctr, int num_sms, cudaStream_t s);
-cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, int group,
+cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt,
+                           const unsigned long long *cand, unsigned long long cand_cap, unsigned long long *raw,
+                           unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
+cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group,
                             unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
 // Sorts raw[0, n) and removes duplicates; *n_unique (device) receives the count.  temp/temp_bytes:
 // scratch from sort_temp_bytes(n).
 size_t sort_temp_bytes(unsigned long long n);
 cudaError_t launch_sort_unique(unsigned long long *raw, unsigned long long *sorted, unsigned long long *uniq,
                                unsigned long long n, unsigned long long *n_unique, void *temp, size_t temp_bytes, cudaStream_t s);
-cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix,
-                           const PodDev *pods, int n_pods, const unsigned long long *uniq, unsigned long long n_events,
-                           EventOut out, cudaStream_t s);
+cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
+                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, cudaStream_t s);
 // Line table of one pod: out[i] = offset (relative to the pod) of line i, i < n_lines.
 cudaError_t launch_line_starts(const uint8_t *text, const unsigned long long *tile_prefix, unsigned long long nl_before, int n_lines,
                                unsigned long long pod_start, unsigned long long pod_eff_end, long long *out, int num_sms, cudaStream_t s);

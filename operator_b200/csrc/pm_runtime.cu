@@ -107,11 +107,25 @@ struct Device {
 
 }  // namespace
 
+// The gram filter hashes with an odd multiplier.  Which text grams collide with the set bits is
+// a matter of luck per (library, workload): when a frequent gram of the logs collides, the
+// candidate rate jumps far above the bitmap's fill rate.  The runtime watches that rate and
+// rebuilds the bitmap with another multiplier (a perf adaptation only: results never depend on
+// it, every candidate is confirmed exactly).
+struct SeedState {
+    int tried = 0;
+    bool settled = false;
+    double best_rate = 1e300;
+    uint32_t best_mult = kFilterMult0;
+    void *dev_bitmap = nullptr;
+};
+
 struct pm_library {
     CompiledLibrary lib;
     std::atomic<int> refs{1};
     std::vector<DeviceLibrary> dev;   // per context device, after publish
     std::vector<void *> dev_blobs;
+    std::vector<SeedState> seed;
     pm_ctx *owner = nullptr;
 };
 
@@ -134,6 +148,7 @@ void lib_unref(pm_library *l) {
             if (l->dev_blobs[d]) {
                 cudaSetDevice(l->owner->devs[d]->id);
                 cudaFree(l->dev_blobs[d]);
+                if (d < l->seed.size() && l->seed[d].dev_bitmap) cudaFree(l->seed[d].dev_bitmap);
             }
         delete l;
     }
@@ -152,7 +167,9 @@ struct DevWork {
     std::vector<int> pods;   // batch pod indices, ascending
     uint64_t total = 0, n_tiles = 0;
     uint64_t cand_cap = 0, raw_cap = 0;
-    Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, raw_end, ev_soa, lines_tmp;
+    Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, ev_soa, lines_tmp;
+    int any_trailing_cr = 0;
+    PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
     cudaStream_t stream = nullptr;
     cudaEvent_t e[8] = {nullptr};   // 0 h2d0, 1 h2d1, 2 scan0, 3 scan1, 4 mid, 5 post0, 6 post1, 7 d2h1
@@ -206,7 +223,7 @@ void release_work(pm_batch *b) {
         Device *d = b->ctx->devs[w.slot];
         cudaSetDevice(d->id);
         if (w.stream) cudaStreamSynchronize(w.stream);
-        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.raw_end, &w.ev_soa, &w.lines_tmp})
+        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp})
             put(d->pool, *x);
         for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa}) put(b->ctx->pinned, *x);
         for (auto &ev : w.e)
@@ -297,17 +314,19 @@ int stage(pm_batch *b) {
         const int np = (int)w.pods.size();
         uint64_t off = kHeaderBytes;
         int rc;
-        if ((rc = get(ctx->pinned, sizeof(PodDev) * (np + 1) + 8 * (np + 1), w.h_pods))) return rc;
+        if ((rc = get(ctx->pinned, sizeof(PodDev) * (np + 1), w.h_pods))) return rc;
         PodDev *hp = w.h_pods.as<PodDev>();
-        unsigned long long *hre = reinterpret_cast<unsigned long long *>(hp + np + 1);
+        w.any_trailing_cr = 0;
         for (int k = 0; k < np; k++) {
             PodRef &p = b->pods[w.pods[k]];
             p.start = off;
             hp[k].start = off;
             hp[k].eff_end = off + p.eff_len;
+            hp[k].raw_end = off + p.len;
             hp[k].nl_before = 0;
             hp[k].n_lines = 0;
-            hre[k] = off + p.len;
+            hp[k].pad = 0;
+            if (p.len && p.ptr[p.len - 1] == '\r') w.any_trailing_cr = 1;
             off = round_up(off + p.len + 1, 16);   // >= 1 byte of '\n' padding
         }
         // content end, rounded to a tile, plus one full tile of '\n' so that 512-byte look-ahead
@@ -325,21 +344,64 @@ int stage(pm_batch *b) {
         if ((rc = get(d->pool, w.raw_cap * 8, w.raw))) return rc;
         if ((rc = get(d->pool, sizeof(ScanCounters) + 64, w.ctr))) return rc;
         if ((rc = get(d->pool, sizeof(PodDev) * (np + 1), w.pods_dev))) return rc;
-        if ((rc = get(d->pool, 8 * (np + 1), w.raw_end))) return rc;
         if ((rc = get(ctx->pinned, sizeof(ScanCounters) + 64, w.h_ctr))) return rc;
         CU(cudaMemcpyAsync(w.pods_dev.p, hp, sizeof(PodDev) * np, cudaMemcpyHostToDevice, w.stream));
-        CU(cudaMemcpyAsync(w.raw_end.p, hre, 8 * np, cudaMemcpyHostToDevice, w.stream));
         CU(cudaEventRecord(w.e[0], w.stream));
         for (int k = 0; k < np; k++) {
             PodRef &p = b->pods[w.pods[k]];
             if (p.len) CU(cudaMemcpyAsync(w.text.as<uint8_t>() + p.start, p.ptr, p.len, cudaMemcpyHostToDevice, w.stream));
         }
         CU(cudaEventRecord(w.e[1], w.stream));
-        CU(launch_pad(w.text.as<uint8_t>(), w.pods_dev.as<PodDev>(), w.raw_end.as<unsigned long long>(), np, w.total, w.stream));
+        CU(launch_pad(w.text.as<uint8_t>(), w.pods_dev.as<PodDev>(), np, w.total, w.stream));
         w.launches = 1;
         w.staged = true;
     }
     b->staged = true;
+    return PM_OK;
+}
+
+const uint32_t kSeedMults[] = {kFilterMult0, 0x85EBCA77u, 0xC2B2AE3Du, 0x27D4EB2Fu, 0x165667B1u, 0xD3A2646Du, 0xFD7046C5u, 0xB55A4F09u};
+
+// Called with the device idle (stream synchronised, device mutex held by the batch).
+int maybe_reseed(pm_library *l, int slot, uint64_t n_cand, uint64_t total_bytes) {
+    const BlobHeader &h = *l->lib.header();
+    if (!h.filter_log2_bits || slot >= (int)l->seed.size()) return PM_OK;
+    SeedState &st = l->seed[slot];
+    if (st.settled || total_bytes < (8u << 20)) return PM_OK;   // small batches say nothing about rates
+    DeviceLibrary &dl = l->dev[slot];
+    const double words = (double)total_bytes / 4.0;
+    const double fill = (double)h.n_grams / (double)(1ull << h.filter_log2_bits);
+    const double rate = (double)n_cand / words;
+    if (rate < st.best_rate) st.best_rate = rate, st.best_mult = dl.mult;
+    const int n_mults = (int)(sizeof(kSeedMults) / sizeof(kSeedMults[0]));
+    uint32_t next;
+    if (rate <= 3.0 * fill + 2e-5) {
+        st.settled = true;
+        return PM_OK;
+    }
+    st.tried++;
+    if (st.tried < n_mults) {
+        next = kSeedMults[st.tried];
+    } else {
+        next = st.best_mult;
+        st.settled = true;
+        if (next == dl.mult) return PM_OK;
+    }
+    // rebuild the bitmap from the gram table with the new multiplier
+    const uint8_t *blob = l->lib.blob.data();
+    const uint32_t *gk = reinterpret_cast<const uint32_t *>(blob + h.off_gram_keys);
+    const size_t nwords = (size_t)(1u << h.filter_log2_bits) / 32;
+    std::vector<uint32_t> bm(nwords, 0);
+    for (uint32_t i = 0; i < (1u << h.gram_log2_cap); i++)
+        if (gk[i] != kGramEmpty) {
+            uint32_t bit = gram_filter_bit(gk[i], h.filter_log2_bits, next);
+            bm[bit >> 5] |= 1u << (bit & 31);
+        }
+    CU(cudaSetDevice(l->owner->devs[slot]->id));
+    if (!st.dev_bitmap) CU(cudaMalloc(&st.dev_bitmap, nwords * 4));
+    CU(cudaMemcpy(st.dev_bitmap, bm.data(), nwords * 4, cudaMemcpyHostToDevice));
+    dl.bitmap = reinterpret_cast<const uint8_t *>(st.dev_bitmap);
+    dl.mult = next;
     return PM_OK;
 }
 
@@ -357,12 +419,12 @@ int scan_async(pm_batch *b) {
         CU(cudaEventRecord(w.e[3], w.stream));
         CU(launch_prefix(w.tile_nl.as<uint32_t>(), w.tile_prefix.as<unsigned long long>(), w.n_tiles, w.scratch.as<unsigned long long>(), w.stream));
         CU(launch_pods(w.text.as<uint8_t>(), w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), np, w.stream));
-        CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.cand.as<unsigned long long>(), w.raw.as<unsigned long long>(), w.raw_cap,
-                          w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
+        CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.raw.as<unsigned long long>(),
+                          w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
         w.launches += 1 + 3 + (np ? 1 : 0) + (dl.h.filter_log2_bits ? 1 : 0);
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
-            CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, (int)g, w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(),
-                               d->num_sms, w.stream));
+            CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, w.table(), (int)g, w.raw.as<unsigned long long>(), w.raw_cap,
+                               w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
             w.launches++;
         }
         CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, sizeof(ScanCounters), cudaMemcpyDeviceToHost, w.stream));
@@ -435,8 +497,8 @@ int finish(pm_batch *b, pm_result_view *out) {
             SoaLayout L(w.n_events);
             if ((rc = get(d->pool, L.bytes, w.ev_soa))) return rc;
             if ((rc = get(ctx->pinned, L.bytes, w.h_soa))) return rc;
-            CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), (int)w.pods.size(),
-                              w.uniq.as<unsigned long long>(), w.n_events, L.on(w.ev_soa.p), w.stream));
+            CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), w.uniq.as<unsigned long long>(),
+                              w.n_events, L.on(w.ev_soa.p), w.stream));
             w.launches += 1;
             CU(cudaEventRecord(w.e[6], w.stream));
             CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
@@ -448,7 +510,7 @@ int finish(pm_batch *b, pm_result_view *out) {
     // ---- phase 2: gather in batch pod order
     uint64_t total_events = 0, bytes = 0, n_cand = 0, n_ver = 0;
     int launches = 0;
-    double ms_h2d = 0, ms_scan = 0, ms_post = 0, ms_d2h = 0;
+    double ms_h2d = 0, ms_scan = 0, ms_post = 0, ms_d2h = 0, ms_total = 0;
     for (auto &w : b->work) {
         CU(cudaSetDevice(ctx->devs[w.slot]->id));
         CU(cudaStreamSynchronize(w.stream));
@@ -458,17 +520,21 @@ int finish(pm_batch *b, pm_result_view *out) {
         n_ver += w.n_verified;
         launches += w.launches;
         w.launches = 0;
-        float a = 0, s = 0, p1 = 0, p2 = 0, dd = 0;
+        float a = 0, s = 0, p1 = 0, p2 = 0, dd = 0, tt = 0;
         cudaEventElapsedTime(&a, w.e[0], w.e[1]);
         cudaEventElapsedTime(&s, w.e[2], w.e[3]);
         cudaEventElapsedTime(&p1, w.e[3], w.e[4]);
         cudaEventElapsedTime(&p2, w.e[5], w.e[6]);
         cudaEventElapsedTime(&dd, w.e[6], w.e[7]);
+        cudaEventElapsedTime(&tt, w.e[2], w.e[7]);
+        ms_total = std::max<double>(ms_total, tt);
         ms_h2d = std::max<double>(ms_h2d, a);
         ms_scan = std::max<double>(ms_scan, s);
         ms_post = std::max<double>(ms_post, p1 + p2);
         ms_d2h = std::max<double>(ms_d2h, dd);
         w.scanned = true;
+        int rs = maybe_reseed(b->lib, w.slot, w.n_cand, w.total);
+        if (rs) return rs;
     }
     const size_t np = b->pods.size();
     SoaLayout L(total_events);
@@ -544,6 +610,7 @@ int finish(pm_batch *b, pm_result_view *out) {
     v.ms_scan = ms_scan;
     v.ms_post = ms_post;
     v.ms_d2h = ms_d2h;
+    v.ms_total = ms_total;
     v.bytes_scanned = (int64_t)bytes;
     v.n_candidates = (int64_t)n_cand;
     v.n_verified = (int64_t)n_ver;
@@ -561,6 +628,36 @@ int pm_abi_version(void) { return PM_ABI_VERSION; }
 
 const char *pm_last_error(void) { return g_err.c_str(); }
 
+int pm_init_devices(const int *device_ids, int n, pm_ctx **out) {
+    if (!out || !device_ids || n <= 0) return fail(PM_E_INVALID, "bad arguments");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return fail(PM_E_NO_DEVICE, "no CUDA device (%s); this engine has no CPU path", e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+    }
+    pm_ctx *ctx = new pm_ctx();
+    ctx->pinned.pinned = true;
+    for (int k = 0; k < n; k++) {
+        int i = device_ids[k];
+        cudaDeviceProp prop;
+        if (i < 0 || i >= count || cudaGetDeviceProperties(&prop, i) != cudaSuccess || prop.major < 10) {
+            cudaGetLastError();
+            for (auto *d : ctx->devs) delete d;
+            delete ctx;
+            return fail(PM_E_NO_DEVICE, "device %d is missing or not sm_100-class: the kernels are built for sm_100a only", i);
+        }
+        Device *d = new Device();
+        d->id = i;
+        d->num_sms = prop.multiProcessorCount;
+        d->pool.device = i;
+        ctx->devs.push_back(d);
+    }
+    *out = ctx;
+    return PM_OK;
+}
+
 int pm_init(int n_devices, pm_ctx **out) {
     if (!out) return fail(PM_E_INVALID, "out is null");
     *out = nullptr;
@@ -571,23 +668,9 @@ int pm_init(int n_devices, pm_ctx **out) {
         return fail(PM_E_NO_DEVICE, "no CUDA device (%s); this engine has no CPU path", e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
     }
     if (n_devices <= 0 || n_devices > count) n_devices = count;
-    pm_ctx *ctx = new pm_ctx();
-    ctx->pinned.pinned = true;
-    for (int i = 0; i < n_devices; i++) {
-        cudaDeviceProp prop;
-        if (cudaGetDeviceProperties(&prop, i) != cudaSuccess || prop.major < 10) {
-            for (auto *d : ctx->devs) delete d;
-            delete ctx;
-            return fail(PM_E_NO_DEVICE, "device %d is not sm_100-class: the kernels are built for sm_100a only", i);
-        }
-        Device *d = new Device();
-        d->id = i;
-        d->num_sms = prop.multiProcessorCount;
-        d->pool.device = i;
-        ctx->devs.push_back(d);
-    }
-    *out = ctx;
-    return PM_OK;
+    std::vector<int> ids(n_devices);
+    for (int i = 0; i < n_devices; i++) ids[i] = i;
+    return pm_init_devices(ids.data(), n_devices, out);
 }
 
 void pm_shutdown(pm_ctx *ctx) {
@@ -633,12 +716,15 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
         l->owner = ctx;
         l->dev.resize(ctx->devs.size());
         l->dev_blobs.assign(ctx->devs.size(), nullptr);
+        l->seed.assign(ctx->devs.size(), SeedState());
         for (size_t d = 0; d < ctx->devs.size(); d++) {
             CU(cudaSetDevice(ctx->devs[d]->id));
             CU(cudaMalloc(&l->dev_blobs[d], l->lib.blob.size()));
             CU(cudaMemcpy(l->dev_blobs[d], l->lib.blob.data(), l->lib.blob.size(), cudaMemcpyHostToDevice));
             l->dev[d].blob = reinterpret_cast<const uint8_t *>(l->dev_blobs[d]);
             l->dev[d].h = *l->lib.header();
+            l->dev[d].bitmap = l->dev[d].blob + l->lib.header()->off_bitmap;
+            l->dev[d].mult = kFilterMult0;
         }
     }
     pm_library *old;

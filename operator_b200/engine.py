@@ -51,7 +51,7 @@ class ResultView(ctypes.Structure):
                 ("ctx_first_line", _P(ctypes.c_int32)), ("ctx_last_line", _P(ctypes.c_int32)),
                 ("ctx_start", _P(ctypes.c_int64)), ("ctx_end", _P(ctypes.c_int64)), ("score", _P(ctypes.c_double)),
                 ("pod_tag", _P(ctypes.c_uint64)), ("pod_first_event", _P(ctypes.c_int64)), ("pod_n_lines", _P(ctypes.c_int32)),
-                ("ms_h2d", ctypes.c_double), ("ms_scan", ctypes.c_double), ("ms_post", ctypes.c_double), ("ms_d2h", ctypes.c_double),
+                ("ms_h2d", ctypes.c_double), ("ms_scan", ctypes.c_double), ("ms_post", ctypes.c_double), ("ms_d2h", ctypes.c_double), ("ms_total", ctypes.c_double),
                 ("bytes_scanned", ctypes.c_int64), ("n_candidates", ctypes.c_int64), ("n_verified", ctypes.c_int64),
                 ("gpu_launches", ctypes.c_int64)]
 
@@ -65,7 +65,7 @@ class ScanError(RuntimeError):
 _dll = None
 
 # every symbol include/podmortem_scan.h declares (tests check the library exports all of them)
-ABI_SYMBOLS = ["pm_abi_version", "pm_init", "pm_shutdown", "pm_last_error", "pm_device_count", "pm_library_compile",
+ABI_SYMBOLS = ["pm_abi_version", "pm_init", "pm_init_devices", "pm_shutdown", "pm_last_error", "pm_device_count", "pm_library_compile",
                "pm_library_publish", "pm_library_free", "pm_library_pattern_count", "pm_library_pattern_meta_json",
                "pm_host_alloc", "pm_host_free", "pm_batch_begin", "pm_batch_add_pod", "pm_batch_submit", "pm_batch_wait",
                "pm_batch_release", "pm_batch_stage", "pm_batch_rescan", "pm_batch_line_index", "pm_parse"]
@@ -83,6 +83,7 @@ def load_library() -> ctypes.CDLL:
     vp, sz = ctypes.c_void_p, ctypes.c_size_t
     d.pm_abi_version.restype = ctypes.c_int
     d.pm_init.argtypes = [ctypes.c_int, _P(vp)]
+    d.pm_init_devices.argtypes = [_P(ctypes.c_int), ctypes.c_int, _P(vp)]
     d.pm_shutdown.argtypes = [vp]
     d.pm_shutdown.restype = None
     d.pm_last_error.restype = ctypes.c_char_p
@@ -144,7 +145,7 @@ class Result:
         self.pod_tag = c(_arr(v.pod_tag, p, np.uint64))
         self.pod_first_event = c(_arr(v.pod_first_event, p + 1, np.int64))
         self.pod_n_lines = c(_arr(v.pod_n_lines, p, np.int32))
-        self.ms_h2d, self.ms_scan, self.ms_post, self.ms_d2h = v.ms_h2d, v.ms_scan, v.ms_post, v.ms_d2h
+        self.ms_h2d, self.ms_scan, self.ms_post, self.ms_d2h, self.ms_total = v.ms_h2d, v.ms_scan, v.ms_post, v.ms_d2h, v.ms_total
         self.bytes_scanned, self.n_candidates, self.n_verified = int(v.bytes_scanned), int(v.n_candidates), int(v.n_verified)
         self.gpu_launches = int(v.gpu_launches)
 
@@ -248,10 +249,14 @@ class Engine:
     """One pm_ctx: the GPUs of this process (one process per GPU under torchrun, or all GPUs of
     the node when used stand-alone)."""
 
-    def __init__(self, n_devices: int = 0):
+    def __init__(self, n_devices: int = 0, devices: Optional[Sequence[int]] = None):
         d = load_library()
         ctx = ctypes.c_void_p()
-        _check(d.pm_init(n_devices, ctypes.byref(ctx)))
+        if devices is not None:
+            ids = (ctypes.c_int * len(devices))(*devices)
+            _check(d.pm_init_devices(ids, len(devices), ctypes.byref(ctx)))
+        else:
+            _check(d.pm_init(n_devices, ctypes.byref(ctx)))
         self._ctx = ctx
 
     @property
