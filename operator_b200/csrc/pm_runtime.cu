@@ -373,6 +373,8 @@ int maybe_reseed(pm_library *l, int slot, uint64_t n_cand, uint64_t total_bytes)
     const double fill = (double)h.n_grams / (double)(1ull << h.filter_log2_bits);
     const double rate = (double)n_cand / words;
     if (rate < st.best_rate) st.best_rate = rate, st.best_mult = dl.mult;
+    if (getenv("PM_DEBUG"))
+        fprintf(stderr, "[pm] filter mult %08x: %llu candidates, rate %.5f (fill %.5f), tried %d\n", dl.mult, (unsigned long long)n_cand, rate, fill, st.tried);
     const int n_mults = (int)(sizeof(kSeedMults) / sizeof(kSeedMults[0]));
     uint32_t next;
     if (rate <= 3.0 * fill + 2e-5) {
