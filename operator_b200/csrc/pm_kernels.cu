@@ -10,7 +10,8 @@
 //   k_confirm     a11: candidate -> exact gram -> literal -> verify DFA on the line -> raw event
 //   k_dfa_scan    a11: combined DFA in shared memory for patterns without a usable literal
 //   sort/unique   ordering + de-duplication of raw events (CUB radix sort, not a hot path)
-//   k_resolve     a12 + a13: line numbers, context ranges, secondary proximity, fp64 score
+//   k_plan / k_check / k_check_long / k_finalize   a12 + a13: line numbers, context ranges,
+//                 secondary proximity, fp64 score
 //   k_line_starts a10: materialised line table of one pod (ballot/prefix-scan scatter)
 #include <cub/cub.cuh>
 
@@ -427,14 +428,33 @@ __global__ void k_mark_unique(const unsigned long long *sorted, unsigned long lo
     if (i < n) flags[i] = (sorted[i] != ~0ull) && (i == 0 || sorted[i] != sorted[i - 1]);
 }
 
-// ------------------------------------------------------------------------------------ k_resolve
-constexpr int kResolveWarps = 2;
+// ------------------------------------------------------------------------------------ resolve (a12 + a13)
+// Three kernels, so that the expensive part -- walking context lines through the STACK and
+// secondary-pattern DFAs -- is balanced over the whole GPU instead of serialised per event:
+//   k_plan       warp per event: line number, context geometry, one work item per
+//                (event, unit, line) that needs a DFA verdict
+//   k_check      thread per item (short lines); k_check_long: warp per item with a speculative
+//                chunked walk (every lane guesses its entry state, guesses are validated in order)
+//   k_finalize   thread per event: STACK run length, nearest secondary hit, fp64 score
+constexpr int kPlanWarps = 2;
 constexpr int kCtxSlots = kMaxCtxLines + 2;
+constexpr uint32_t kItemInvalid = 0xFFFFFFFFu;
+constexpr uint32_t kLongLine = 512;      // lines above this are walked by a whole warp
+
+struct Item {
+    unsigned long long a;    // line start in text
+    uint32_t len;            // kItemInvalid: the line does not exist (outside the pod)
+    uint32_t unit;
+};
+
+struct EvAux {
+    unsigned long long item_base;
+    int32_t n_stack, na;
+};
 
 // Collects positions of the next `need` '\n' bytes at positions >= from into out[0..need).
 __device__ void warp_collect_forward(const uint8_t *text, unsigned long long from, int need, unsigned long long *out) {
     const int lane = threadIdx.x & 31;
-    const unsigned lt = lanemask_lt();
     unsigned long long a0 = from & ~15ull;
     int got = 0;
     while (got < need) {
@@ -443,7 +463,6 @@ __device__ void warp_collect_forward(const uint8_t *text, unsigned long long fro
         uint32_t m = newline_mask16(v);
         if (a < from) m &= (from - a >= 16) ? 0u : ~((1u << (from - a)) - 1u);
         int c = __popc(m);
-        // exclusive prefix over lanes via ballots of the counts' bits is overkill: use shfl scan
         int inc = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -458,7 +477,6 @@ __device__ void warp_collect_forward(const uint8_t *text, unsigned long long fro
         }
         got += __shfl_sync(FULL, inc, 31);
         a0 += 512;
-        (void)lt;
     }
     __syncwarp();
 }
@@ -497,24 +515,24 @@ __device__ void warp_collect_backward(const uint8_t *text, unsigned long long be
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(kResolveWarps * 32) k_resolve(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
-                                                                const unsigned long long *__restrict__ tile_prefix, PodTable pt,
-                                                                const unsigned long long *__restrict__ uniq, unsigned long long n_events, EventOut out) {
-    const PodDev *pods = pt.pods;
-    const int n_pods = pt.n;
-    __shared__ unsigned long long fwd_s[kResolveWarps][kCtxSlots];   // fwd[i]: '\n' that ends line L+i
-    __shared__ unsigned long long bwd_s[kResolveWarps][kCtxSlots];   // bwd[i]: '\n' that precedes line L-i
+__global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
+                                                          const unsigned long long *__restrict__ tile_prefix, PodTable pt,
+                                                          const unsigned long long *__restrict__ uniq, unsigned long long n_events, EventOut out,
+                                                          Item *__restrict__ items, unsigned long long item_cap, uint32_t *__restrict__ long_list,
+                                                          unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr) {
+    __shared__ unsigned long long fwd_s[kPlanWarps][kCtxSlots];   // fwd[i]: '\n' that ends line L+i
+    __shared__ unsigned long long bwd_s[kPlanWarps][kCtxSlots];   // bwd[i]: '\n' that precedes line L-i
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned long long *fwd = fwd_s[warp], *bwd = bwd_s[warp];
     const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
+    const PodDev *pods = pt.pods;
 
-    for (unsigned long long ev = (unsigned long long)blockIdx.x * kResolveWarps + warp; ev < n_events; ev += (unsigned long long)gridDim.x * kResolveWarps) {
+    for (unsigned long long ev = (unsigned long long)blockIdx.x * kPlanWarps + warp; ev < n_events; ev += (unsigned long long)gridDim.x * kPlanWarps) {
         const unsigned long long key = uniq[ev], ls = key >> kPatternBits;
         const uint32_t pat = (uint32_t)(key & ((1u << kPatternBits) - 1u));
         const PatternDesc pd = pds[pat];
-        // pod = last pod with start <= ls
-        int lo = 0, hi = n_pods - 1;
+        int lo = 0, hi = pt.n - 1;   // pod = last pod with start <= ls
         while (lo < hi) {
             int mid = (lo + hi + 1) >> 1;
             if (pods[mid].start <= ls) lo = mid; else hi = mid - 1;
@@ -524,12 +542,15 @@ __global__ void __launch_bounds__(kResolveWarps * 32) k_resolve(const uint8_t *_
         const long long n_lines = pod.n_lines;
         const int nb = (int)min((long long)pd.lines_before, L - 1);
         const int na = (int)min((long long)pd.lines_after, n_lines - L);
-        int need_f = na, need_b = nb;
-        if (pd.include_stack) need_f = max(need_f, (int)min((long long)kStackMax, n_lines - L));
+        const int stack_cap = pd.include_stack ? (int)min((long long)kStackMax, n_lines - L) : 0;
+        const int n_stack = max(0, stack_cap - na);
+        int need_f = max(na, stack_cap), need_b = nb;
+        unsigned long long n_items = (unsigned long long)n_stack;
         for (uint32_t j = 0; j < pd.sec_count; j++) {
             int w = sds[pd.sec_first + j].window;
             need_f = max(need_f, (int)min((long long)w, n_lines - L));
             need_b = max(need_b, (int)min((long long)w, L - 1));
+            n_items += 2ull * w + 1;
         }
         warp_collect_forward(text, ls, need_f + 1, fwd);
         if (lane == 0) bwd[0] = ls - 1;
@@ -547,77 +568,172 @@ __global__ void __launch_bounds__(kResolveWarps * 32) k_resolve(const uint8_t *_
             if (b > a && text[b - 1] == '\r' && !(pt.any_trailing_cr && b == pod.raw_end)) b--;
         };
 
-        // ---- context (a13)
-        int last_rel = na;
-        if (pd.include_stack && na < kStackMax) {
-            const int cap_rel = (int)min((long long)kStackMax, n_lines - L);
-            UnitTables st = unit_tables(blob, h, h.stack_unit);
-            // lines L+na+1 .. L+cap_rel, 32 at a time; stop at the first non-stack line
-            for (int r0 = na + 1; r0 <= cap_rel; r0 += 32) {
-                int rel = r0 + lane;
-                bool ok = false;
-                if (rel <= cap_rel) {
-                    unsigned long long a, b;
-                    line_span(rel, a, b);
-                    ok = line_matches(text, a, b, st);
+        unsigned long long base = 0;
+        if (lane == 0 && n_items) base = atomicAdd(&ctr->n_items, n_items);
+        base = __shfl_sync(FULL, base, 0);
+        const bool fits = base + n_items <= item_cap;
+        if (!fits && lane == 0) ctr->overflow = 1;
+
+        if (fits) {
+            // STACK items: lines L+na+1 .. L+stack_cap
+            for (int k = lane; k < n_stack; k += 32) {
+                unsigned long long a, b;
+                line_span(na + 1 + k, a, b);
+                Item it{a, (uint32_t)(b - a), h.stack_unit};
+                items[base + k] = it;
+                if (it.len > kLongLine) {
+                    unsigned long long at = atomicAdd(&ctr->n_long, 1ull);
+                    if (at < long_cap) long_list[at] = (uint32_t)(base + k); else ctr->overflow = 1;
                 }
-                unsigned good = __ballot_sync(FULL, ok);
-                int run = __ffs(~good) - 1;   // leading lanes that are stack lines (32 if all)
-                if (run < 0) run = 32;
-                int avail = min(32, cap_rel - r0 + 1);
-                run = min(run, avail);
-                last_rel = r0 + run - 1;
-                if (run < 32) break;
             }
-            last_rel = max(last_rel, na);
-        }
-        // ---- score (a12): secondaries in order, nearest matching line within the window
-        double acc = 0.0;
-        for (uint32_t j = 0; j < pd.sec_count; j++) {
-            const SecDesc sd = sds[pd.sec_first + j];
-            UnitTables ut = unit_tables(blob, h, sd.unit);
-            int best = 0x7FFFFFFF;
-            for (int i0 = 0; i0 < 2 * sd.window + 1; i0 += 32) {
-                int idx = i0 + lane;
-                if (idx < 2 * sd.window + 1) {
+            // secondary items: idx 0..2w, distance d = (idx+1)/2, odd idx = before, even = after
+            unsigned long long off = base + n_stack;
+            for (uint32_t j = 0; j < pd.sec_count; j++) {
+                const SecDesc sd = sds[pd.sec_first + j];
+                const int cnt = 2 * sd.window + 1;
+                for (int idx = lane; idx < cnt; idx += 32) {
                     int d = (idx + 1) >> 1;
                     int rel = (idx & 1) ? -d : d;
                     bool valid = rel >= 0 ? (d <= n_lines - L) : (d <= L - 1);
-                    if (valid && d < best) {
+                    Item it{0, kItemInvalid, sd.unit};
+                    if (valid) {
                         unsigned long long a, b;
                         line_span(rel, a, b);
-                        if (line_matches(text, a, b, ut)) best = d;
+                        it.a = a;
+                        it.len = (uint32_t)(b - a);
+                    }
+                    items[off + idx] = it;
+                    if (valid && it.len > kLongLine) {
+                        unsigned long long at = atomicAdd(&ctr->n_long, 1ull);
+                        if (at < long_cap) long_list[at] = (uint32_t)(off + idx); else ctr->overflow = 1;
                     }
                 }
-                int wbest = __reduce_min_sync(FULL, best);
-                if (wbest != 0x7FFFFFFF) {   // distances only grow with i0
-                    best = wbest;
-                    break;
-                }
-            }
-            best = __reduce_min_sync(FULL, best);
-            if (best != 0x7FFFFFFF) {
-                double term = __dmul_rn(sd.weight, __dsub_rn(1.0, __ddiv_rn((double)best, (double)(sd.window + 1))));
-                acc = __dadd_rn(acc, term);
+                off += cnt;
             }
         }
         if (lane == 0) {
             unsigned long long la, lb, ca, cb, ea, eb;
             line_span(0, la, lb);
             line_span(-nb, ca, cb);
-            line_span(last_rel, ea, eb);
+            line_span(na, ea, eb);
             out.pod[ev] = lo;
             out.pattern[ev] = (int32_t)pat;
             out.line_no[ev] = (int32_t)L;
             out.line_start[ev] = (int64_t)(ls - pod.start);
             out.line_len[ev] = (int32_t)(lb - la);
             out.ctx_first[ev] = (int32_t)(L - nb);
-            out.ctx_last[ev] = (int32_t)(L + last_rel);
+            out.ctx_last[ev] = (int32_t)(L + na);            // k_finalize adds the STACK run
             out.ctx_start[ev] = (int64_t)(ca - pod.start);
             out.ctx_end[ev] = (int64_t)(eb - pod.start);
-            out.score[ev] = __dmul_rn(__dmul_rn(pd.confidence, pd.mult), __dadd_rn(1.0, acc));
+            EvAux ax{base, n_stack, na};
+            aux[ev] = ax;
         }
         __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_check(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h, const Item *__restrict__ items,
+                                               unsigned long long item_cap, unsigned char *__restrict__ results, const ResolveCounters *ctr) {
+    if (ctr->overflow) return;
+    const unsigned long long n = ctr->n_items < item_cap ? ctr->n_items : item_cap;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const Item it = items[i];
+        if (it.len == kItemInvalid) {
+            results[i] = 0;
+        } else if (it.len <= kLongLine) {
+            UnitTables ut = unit_tables(blob, h, it.unit);
+            results[i] = line_matches(text, it.a, it.a + it.len, ut);
+        }
+    }
+}
+
+// One warp walks one long line.  Lane i owns bytes [a + i*c, a + (i+1)*c).  Lane 0 starts in
+// the exact start-of-line state; every other lane GUESSES its entry state by warming up from
+// the DFA's mid-line idle state over the 32 bytes in front of its chunk.  The guesses are then
+// validated in lane order: where a guess equals the true exit state of the previous chunk the
+// lane's walk stands, otherwise that one chunk is walked again from the true state.  The result
+// is exact; speculation only shortens the critical path (log text leaves search DFAs idle).
+__global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h, const Item *__restrict__ items,
+                                                    const uint32_t *__restrict__ long_list, unsigned long long long_cap, unsigned char *__restrict__ results,
+                                                    const ResolveCounters *ctr) {
+    if (ctr->overflow) return;
+    const int lane = threadIdx.x & 31;
+    const unsigned long long n = ctr->n_long < long_cap ? ctr->n_long : long_cap;
+    const unsigned long long n_warps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+    for (unsigned long long k = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < n; k += n_warps) {
+        const uint32_t idx = long_list[k];
+        const Item it = items[idx];
+        const UnitDesc *ud = reinterpret_cast<const UnitDesc *>(blob + h.off_units) + it.unit;
+        UnitTables ut = unit_tables(blob, h, it.unit);
+        const uint32_t mid = ud->pad;   // mid-line idle state (pm_library.cc)
+        const unsigned long long a = it.a, b = it.a + it.len;
+        const unsigned long long c = (it.len + 31) / 32;
+        const unsigned long long ca = min(b, a + lane * c), cb = min(b, ca + c);
+        auto walk = [&](uint32_t s, unsigned long long p0, unsigned long long p1) {
+            for (unsigned long long p = p0; p < p1 && s != ut.accept; p++) s = ut.tab[s * ut.stride + ut.cmap[text[p]]];
+            return s;
+        };
+        uint32_t in_spec;
+        if (lane == 0 || ca - a <= 32) {
+            in_spec = walk(0, a, ca);                       // exact: walked from the line start
+        } else {
+            in_spec = walk(mid, ca - 32, ca);
+        }
+        uint32_t out_spec = walk(in_spec, ca, cb);
+        uint32_t truth = 0;                                 // true state at the start of chunk i
+        for (int i = 0; i < 32; i++) {
+            uint32_t in_i = __shfl_sync(FULL, in_spec, i), out_i = __shfl_sync(FULL, out_spec, i);
+            if (in_i != truth) {                            // mis-speculated chunk: redo it (warp-uniform branch)
+                uint32_t redo = 0;
+                if (lane == i) redo = walk(truth, ca, cb);
+                out_i = __shfl_sync(FULL, redo, i);
+            }
+            truth = out_i;
+            if (truth == ut.accept) break;
+        }
+        if (truth != ut.accept) truth = ut.tab[truth * ut.stride + ut.stride - 1];
+        if (lane == 0) results[idx] = (truth == ut.accept);
+    }
+}
+
+__global__ void __launch_bounds__(128) k_finalize(const uint8_t *__restrict__ blob, BlobHeader h, const unsigned long long *__restrict__ uniq,
+                                                  unsigned long long n_events, EventOut out, const Item *__restrict__ items,
+                                                  const unsigned char *__restrict__ results, const EvAux *__restrict__ aux, const PodTable pt,
+                                                  const ResolveCounters *ctr) {
+    if (ctr->overflow) return;
+    const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
+    const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
+    for (unsigned long long ev = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; ev < n_events; ev += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint32_t pat = (uint32_t)(uniq[ev] & ((1u << kPatternBits) - 1u));
+        const PatternDesc pd = pds[pat];
+        const EvAux ax = aux[ev];
+        // context: leading run of STACK lines after the lines_after window
+        int run = 0;
+        while (run < ax.n_stack && results[ax.item_base + run]) run++;
+        if (run > 0) {
+            const Item it = items[ax.item_base + run - 1];
+            out.ctx_last[ev] += run;
+            out.ctx_end[ev] = (int64_t)(it.a + it.len - pt.pods[out.pod[ev]].start);
+        }
+        // score: secondaries in order, nearest matching line (SPEC.md section 5)
+        double acc = 0.0;
+        unsigned long long off = ax.item_base + ax.n_stack;
+        for (uint32_t j = 0; j < pd.sec_count; j++) {
+            const SecDesc sd = sds[pd.sec_first + j];
+            const int cnt = 2 * sd.window + 1;
+            int best = -1;
+            for (int idx = 0; idx < cnt; idx++)
+                if (results[off + idx]) {
+                    best = (idx + 1) >> 1;   // idx ascending = distance non-decreasing
+                    break;
+                }
+            if (best >= 0) {
+                double term = __dmul_rn(sd.weight, __dsub_rn(1.0, __ddiv_rn((double)best, (double)(sd.window + 1))));
+                acc = __dadd_rn(acc, term);
+            }
+            off += cnt;
+        }
+        out.score[ev] = __dmul_rn(__dmul_rn(pd.confidence, pd.mult), __dadd_rn(1.0, acc));
     }
 }
 
@@ -760,12 +876,24 @@ cudaError_t launch_sort_unique(unsigned long long *raw, unsigned long long *sort
     return cub::DeviceSelect::Flagged(cub_temp, cub_bytes, sorted, flags, uniq, n_unique, (long long)n, s);
 }
 
+size_t resolve_item_bytes() { return sizeof(Item); }
+size_t resolve_aux_bytes() { return sizeof(EvAux); }
+
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
-                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, cudaStream_t s) {
+                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, const ResolveScratch &rs, int num_sms,
+                           cudaStream_t s) {
     if (n_events == 0) return cudaSuccess;
-    unsigned blocks = (unsigned)((n_events + kResolveWarps - 1) / kResolveWarps);
-    if (blocks > 148u * 16u) blocks = 148u * 16u;
-    k_resolve<<<blocks, kResolveWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events, out);
+    cudaError_t e = cudaMemsetAsync(rs.ctr, 0, sizeof(ResolveCounters), s);
+    if (e != cudaSuccess) return e;
+    unsigned blocks = (unsigned)((n_events + kPlanWarps - 1) / kPlanWarps);
+    if (blocks > (unsigned)num_sms * 16u) blocks = (unsigned)num_sms * 16u;
+    Item *items = reinterpret_cast<Item *>(rs.items);
+    k_plan<<<blocks, kPlanWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events, out, items, rs.item_cap, rs.long_list, rs.long_cap,
+                                              reinterpret_cast<EvAux *>(rs.aux), rs.ctr);
+    k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
+    k_check_long<<<num_sms * 8, 128, 0, s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
+    unsigned fb = (unsigned)((n_events + 127) / 128);
+    k_finalize<<<fb, 128, 0, s>>>(lib.blob, lib.h, uniq, n_events, out, items, rs.results, reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);
     return cudaGetLastError();
 }
 

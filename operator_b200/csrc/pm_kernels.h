@@ -79,8 +79,28 @@ cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes,
 size_t sort_temp_bytes(unsigned long long n);
 cudaError_t launch_sort_unique(unsigned long long *raw, unsigned long long *sorted, unsigned long long *uniq,
                                unsigned long long n, unsigned long long *n_unique, void *temp, size_t temp_bytes, cudaStream_t s);
+// Resolve stage scratch (device memory owned by the caller).  items: item_cap x resolve_item_bytes(),
+// results: item_cap bytes, long_list: long_cap u32, aux: n_events x resolve_aux_bytes().
+struct ResolveCounters {
+    unsigned long long n_items, n_long;
+    unsigned int overflow, pad;
+};
+struct ResolveScratch {
+    void *items;
+    unsigned long long item_cap;
+    unsigned char *results;
+    uint32_t *long_list;
+    unsigned long long long_cap;
+    void *aux;
+    ResolveCounters *ctr;
+};
+size_t resolve_item_bytes();
+size_t resolve_aux_bytes();
+// Four launches (k_plan, k_check, k_check_long, k_finalize).  If rs.ctr->overflow is set afterwards the
+// scratch was too small and the outputs are incomplete: call again with larger capacities.
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
-                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, cudaStream_t s);
+                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, const ResolveScratch &rs, int num_sms,
+                           cudaStream_t s);
 // Line table of one pod: out[i] = offset (relative to the pod) of line i, i < n_lines.
 cudaError_t launch_line_starts(const uint8_t *text, const unsigned long long *tile_prefix, unsigned long long nl_before, int n_lines,
                                unsigned long long pod_start, unsigned long long pod_eff_end, long long *out, int num_sms, cudaStream_t s);

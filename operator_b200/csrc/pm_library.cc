@@ -336,6 +336,9 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
             u.nstates = (uint16_t)d.nstates;
             u.stride = (uint16_t)d.stride();
             u.accept_state = (uint16_t)d.first_accept;   // early-accept: one sticky state
+            // mid-line idle state: where the DFA sits after one byte that belongs to no pattern;
+            // the entry-state guess of the speculative long-line walk (k_check_long)
+            u.pad = d.next[(size_t)d.classmap[0x01]];
             if (d.first_accept >= d.nstates)
                 throw CompileFail{PM_E_UNSUPPORTED, -1, -1, -1, "", "regex can never match"};
             units_sec.push(u);

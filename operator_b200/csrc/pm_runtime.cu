@@ -168,6 +168,8 @@ struct DevWork {
     uint64_t total = 0, n_tiles = 0;
     uint64_t cand_cap = 0, raw_cap = 0;
     Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, ev_soa, lines_tmp;
+    Buf rs_items, rs_results, rs_long, rs_aux, rs_ctr, h_rs_ctr;   // resolve-stage scratch
+    uint64_t item_cap = 0, long_cap = 0;
     int any_trailing_cr = 0;
     PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
@@ -223,9 +225,9 @@ void release_work(pm_batch *b) {
         Device *d = b->ctx->devs[w.slot];
         cudaSetDevice(d->id);
         if (w.stream) cudaStreamSynchronize(w.stream);
-        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp})
+        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.rs_ctr})
             put(d->pool, *x);
-        for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa}) put(b->ctx->pinned, *x);
+        for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa, &w.h_rs_ctr}) put(b->ctx->pinned, *x);
         for (auto &ev : w.e)
             if (ev) cudaEventDestroy(ev), ev = nullptr;
         if (w.stream) cudaStreamDestroy(w.stream), w.stream = nullptr;
@@ -488,26 +490,57 @@ int finish(pm_batch *b, pm_result_view *out) {
         }
         (void)dl;
     }
-    for (auto &w : b->work) {
+    // resolve stage: sized from the event count; reruns with larger scratch if the work-item
+    // queue overflowed (the flag is read together with the results)
+    auto launch_resolve_for = [&](DevWork &w) -> int {
         Device *d = ctx->devs[w.slot];
         CU(cudaSetDevice(d->id));
-        CU(cudaStreamSynchronize(w.stream));
         const DeviceLibrary &dl = b->lib->dev[w.slot];
-        w.n_events = *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + sizeof(ScanCounters));
         int rc;
         if (w.n_events) {
             SoaLayout L(w.n_events);
+            if (!w.item_cap) w.item_cap = w.n_events * 96 + (1u << 16);
+            if (!w.long_cap) w.long_cap = w.item_cap / 8 + (1u << 12);
+            w.item_cap = std::min<uint64_t>(w.item_cap, 0xFFFFFFF0ull);
             if ((rc = get(d->pool, L.bytes, w.ev_soa))) return rc;
             if ((rc = get(ctx->pinned, L.bytes, w.h_soa))) return rc;
+            if ((rc = get(d->pool, w.item_cap * resolve_item_bytes(), w.rs_items))) return rc;
+            if ((rc = get(d->pool, w.item_cap, w.rs_results))) return rc;
+            if ((rc = get(d->pool, w.long_cap * 4, w.rs_long))) return rc;
+            if ((rc = get(d->pool, w.n_events * resolve_aux_bytes(), w.rs_aux))) return rc;
+            if ((rc = get(d->pool, sizeof(ResolveCounters), w.rs_ctr))) return rc;
+            if ((rc = get(ctx->pinned, sizeof(ResolveCounters), w.h_rs_ctr))) return rc;
+            ResolveScratch rs{w.rs_items.p, w.item_cap, w.rs_results.as<unsigned char>(), w.rs_long.as<uint32_t>(), w.long_cap, w.rs_aux.p,
+                              w.rs_ctr.as<ResolveCounters>()};
             CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), w.uniq.as<unsigned long long>(),
-                              w.n_events, L.on(w.ev_soa.p), w.stream));
-            w.launches += 1;
+                              w.n_events, L.on(w.ev_soa.p), rs, d->num_sms, w.stream));
+            w.launches += 4;
             CU(cudaEventRecord(w.e[6], w.stream));
             CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
+            CU(cudaMemcpyAsync(w.h_rs_ctr.p, w.rs_ctr.p, sizeof(ResolveCounters), cudaMemcpyDeviceToHost, w.stream));
         } else {
             CU(cudaEventRecord(w.e[6], w.stream));
         }
         CU(cudaEventRecord(w.e[7], w.stream));
+        return PM_OK;
+    };
+    for (auto &w : b->work) {
+        CU(cudaSetDevice(ctx->devs[w.slot]->id));
+        CU(cudaStreamSynchronize(w.stream));
+        w.n_events = *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + sizeof(ScanCounters));
+        int rc = launch_resolve_for(w);
+        if (rc) return rc;
+    }
+    for (auto &w : b->work) {
+        while (w.n_events) {
+            CU(cudaSetDevice(ctx->devs[w.slot]->id));
+            CU(cudaStreamSynchronize(w.stream));
+            if (!w.h_rs_ctr.as<ResolveCounters>()->overflow) break;
+            w.item_cap *= 4;
+            w.long_cap *= 4;
+            int rc = launch_resolve_for(w);
+            if (rc) return rc;
+        }
     }
     // ---- phase 2: gather in batch pod order
     uint64_t total_events = 0, bytes = 0, n_cand = 0, n_ver = 0;
