@@ -53,16 +53,16 @@ __device__ __forceinline__ unsigned lanemask_lt() {
 
 // ------------------------------------------------------------------------------------ k_scan
 template <int BITS, bool FOLD>
-__device__ __forceinline__ uint32_t filter_word(uint32_t w, const uint32_t *bm, uint32_t mult) {
+__device__ __forceinline__ uint32_t filter_word(uint32_t w, const uint32_t *bm) {
     uint32_t g = FOLD ? (w | 0x20202020u) : w;
-    uint32_t bit = (g * mult) >> (32 - BITS);
+    uint32_t bit = (g * kFilterMult0) >> (32 - BITS);
     return (bm[bit >> 5] >> (bit & 31u)) & 1u;
 }
 
 template <int BITS, bool FOLD>
 __global__ void __launch_bounds__(kScanThreads, 1)
 k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g,
-       uint32_t mult, uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+       uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
        ScanCounters *__restrict__ ctr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int kBitmapWords = (1 << BITS) / 32;
@@ -90,8 +90,8 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
             uint32_t f0 = not_newline_flags(v[j].x), f1 = not_newline_flags(v[j].y);
             uint32_t f2 = not_newline_flags(v[j].z), f3 = not_newline_flags(v[j].w);
             nz += __popc(f0 | (f1 >> 1) | (f2 >> 2) | (f3 >> 3));
-            uint32_t m4 = filter_word<BITS, FOLD>(v[j].x, bm, mult) | (filter_word<BITS, FOLD>(v[j].y, bm, mult) << 1) |
-                          (filter_word<BITS, FOLD>(v[j].z, bm, mult) << 2) | (filter_word<BITS, FOLD>(v[j].w, bm, mult) << 3);
+            uint32_t m4 = filter_word<BITS, FOLD>(v[j].x, bm) | (filter_word<BITS, FOLD>(v[j].y, bm) << 1) |
+                          (filter_word<BITS, FOLD>(v[j].z, bm) << 2) | (filter_word<BITS, FOLD>(v[j].w, bm) << 3);
             unsigned b = __ballot_sync(FULL, m4 != 0);
             if (b) {   // warp-uniform, rare: stage (group, mask) entries, flush 32 at a time
                 if (m4) wq[qn + __popc(b & lt)] = ((t * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
@@ -307,17 +307,15 @@ __global__ void k_pods(const uint8_t *text, const unsigned long long *tile_prefi
 
 // ------------------------------------------------------------------------------------ k_confirm
 __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h,
-                                                 PodTable pt, const unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+                                                 FilterView fv, PodTable pt, const unsigned long long *__restrict__ cand, unsigned long long cand_cap,
                                                  unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
     if (ctr->cand_overflow) return;   // the host reruns the scan with a larger queue
     const unsigned long long n = ctr->n_cand < cand_cap ? ctr->n_cand : cand_cap;
-    const uint32_t *gk = reinterpret_cast<const uint32_t *>(blob + h.off_gram_keys);
-    const uint32_t *gf = reinterpret_cast<const uint32_t *>(blob + h.off_gram_first);
-    const uint32_t *gc = reinterpret_cast<const uint32_t *>(blob + h.off_gram_count);
-    const Probe *probes = reinterpret_cast<const Probe *>(blob + h.off_probes);
-    const uint8_t *litpool = blob + h.off_litpool;
+    const uint32_t *gk = fv.gkeys, *gf = fv.gfirst, *gc = fv.gcount;
+    const Probe *probes = fv.probes;
+    const uint8_t *litpool = fv.litpool;
     const PatternDesc *pd = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
-    const uint32_t cap_mask = (1u << h.gram_log2_cap) - 1u;
+    const uint32_t cap_mask = (1u << fv.log2_cap) - 1u;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
         unsigned long long e = cand[i];
         unsigned long long group = e >> 4;
@@ -327,8 +325,8 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
             m4 &= m4 - 1;
             unsigned long long p = group * 16 + k * 4;
             uint32_t g = *reinterpret_cast<const uint32_t *>(text + p);
-            if (h.filter_fold) g |= 0x20202020u;
-            uint32_t slot = gram_table_slot(g, h.gram_log2_cap);
+            if (fv.fold) g |= 0x20202020u;
+            uint32_t slot = gram_table_slot(g, fv.log2_cap);
             uint32_t key;
             while ((key = gk[slot]) != g && key != kGramEmpty) slot = (slot + 1) & cap_mask;
             if (key != g) continue;   // bitmap collision
@@ -360,6 +358,26 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
                         ctr->raw_overflow = 1;
                 }
             }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ k_gram_profile
+// Occurrence counts of literal grams in a text sample.  Streams the sample like k_scan (one
+// aligned word per filter probe position) and looks every word up in an open-addressing table
+// that lives in L2; hits are rare, so the atomics are cheap.
+__global__ void __launch_bounds__(256) k_gram_profile(const uint4 *__restrict__ text, unsigned long long n_groups, const uint32_t *__restrict__ keys,
+                                                      uint32_t log2_cap, uint32_t fold, unsigned int *__restrict__ counts) {
+    const uint32_t mask = (1u << log2_cap) - 1u;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_groups; i += (unsigned long long)gridDim.x * blockDim.x) {
+        uint4 v = ld_stream16(text + i);
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            uint32_t g = fold ? (w[k] | 0x20202020u) : w[k];
+            uint32_t slot = gram_table_slot(g, log2_cap), key;
+            while ((key = __ldg(keys + slot)) != g && key != kGramEmpty) slot = (slot + 1) & mask;
+            if (key == g) atomicAdd(counts + slot, 1u);
         }
     }
 }
@@ -776,18 +794,18 @@ __global__ void __launch_bounds__(256) k_line_starts(const uint8_t *__restrict__
 }
 
 template <int BITS>
-cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, uint32_t mult, uint32_t *tile_nl, unsigned long long *cand,
+cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, uint32_t *tile_nl, unsigned long long *cand,
                              unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
     size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
     cudaError_t e;
     if (fold) {
         e = cudaFuncSetAttribute(k_scan<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
     } else {
         e = cudaFuncSetAttribute(k_scan<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
     }
     return cudaGetLastError();
 }
@@ -802,20 +820,19 @@ cudaError_t launch_pad(uint8_t *text, const PodDev *pods, int n_pods, unsigned l
 
 cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const DeviceLibrary &lib, uint32_t *tile_nl, unsigned long long *cand,
                         unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
-    const BlobHeader &h = lib.h;
-    if (h.filter_log2_bits == 0) {
+    const FilterView &fv = lib.fv;
+    if (fv.log2_bits == 0) {
         k_scan_nl_only<<<num_sms, kScanThreads, 0, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, tile_nl);
         return cudaGetLastError();
     }
-    const uint4 *bitmap = reinterpret_cast<const uint4 *>(lib.bitmap);
-    const uint32_t mult = lib.mult;
-    switch (h.filter_log2_bits) {
-        case 15: return launch_scan_bits<15>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 16: return launch_scan_bits<16>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 17: return launch_scan_bits<17>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 18: return launch_scan_bits<18>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 19: return launch_scan_bits<19>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 20: return launch_scan_bits<20>(h.filter_fold, text, n_tiles, bitmap, mult, tile_nl, cand, cand_cap, ctr, num_sms, s);
+    const uint4 *bitmap = reinterpret_cast<const uint4 *>(fv.bitmap);
+    switch (fv.log2_bits) {
+        case 15: return launch_scan_bits<15>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 16: return launch_scan_bits<16>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 17: return launch_scan_bits<17>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 18: return launch_scan_bits<18>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 19: return launch_scan_bits<19>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 20: return launch_scan_bits<20>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
         default: return cudaErrorInvalidValue;
     }
 }
@@ -838,8 +855,8 @@ cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_pref
 
 cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, const unsigned long long *cand,
                            unsigned long long cand_cap, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
-    if (lib.h.filter_log2_bits == 0) return cudaSuccess;
-    k_confirm<<<num_sms * 4, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, pt, cand, cand_cap, raw, raw_cap, ctr);
+    if (lib.fv.log2_bits == 0) return cudaSuccess;
+    k_confirm<<<num_sms * 4, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, lib.fv, pt, cand, cand_cap, raw, raw_cap, ctr);
     return cudaGetLastError();
 }
 
@@ -874,6 +891,12 @@ cudaError_t launch_sort_unique(unsigned long long *raw, unsigned long long *sort
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     return cub::DeviceSelect::Flagged(cub_temp, cub_bytes, sorted, flags, uniq, n_unique, (long long)n, s);
+}
+
+cudaError_t launch_gram_profile(const uint8_t *text, unsigned long long sample_bytes, const uint32_t *keys, uint32_t log2_cap, uint32_t fold,
+                                unsigned int *counts, int num_sms, cudaStream_t s) {
+    k_gram_profile<<<num_sms * 8, 256, 0, s>>>(reinterpret_cast<const uint4 *>(text), sample_bytes / 16, keys, log2_cap, fold, counts);
+    return cudaGetLastError();
 }
 
 size_t resolve_item_bytes() { return sizeof(Item); }

@@ -23,10 +23,18 @@ constexpr int kHeaderBytes = 16;
 constexpr int kPatternBits = 24;        // raw event key = line_start << 24 | pattern
 constexpr int kMaxCtxLines = 1000;      // lines_before / lines_after / proximity_window limit
 
+// The gram filter in use on one device: device pointers into the blob as compiled, or into a
+// separately uploaded rebuild (profile-guided re-selection, pm_runtime.cu).
+struct FilterView {
+    const uint32_t *bitmap = nullptr, *gkeys = nullptr, *gfirst = nullptr, *gcount = nullptr;
+    const Probe *probes = nullptr;
+    const uint8_t *litpool = nullptr;
+    uint32_t log2_bits = 0, log2_cap = 0, fold = 0, n_grams = 0;
+};
+
 struct DeviceLibrary {
     const uint8_t *blob = nullptr;      // device copy of the compiled blob
-    const uint8_t *bitmap = nullptr;    // device gram filter in use (inside the blob, or a reseeded copy)
-    uint32_t mult = 0;                  // odd multiplier the bitmap was built with
+    FilterView fv;
     BlobHeader h;                       // host copy of the blob header
 };
 
@@ -101,6 +109,11 @@ size_t resolve_aux_bytes();
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
                            const unsigned long long *uniq, unsigned long long n_events, EventOut out, const ResolveScratch &rs, int num_sms,
                            cudaStream_t s);
+// Gram profile: counts, for every aligned word of text[0, sample_bytes), the occurrences of the
+// keys of an open-addressing table (keys: 2^log2_cap u32, kGramEmpty = free; counts zeroed by the
+// caller).  Used once per library to learn which literal grams are frequent in the real logs.
+cudaError_t launch_gram_profile(const uint8_t *text, unsigned long long sample_bytes, const uint32_t *keys, uint32_t log2_cap, uint32_t fold,
+                                unsigned int *counts, int num_sms, cudaStream_t s);
 // Line table of one pod: out[i] = offset (relative to the pod) of line i, i < n_lines.
 cudaError_t launch_line_starts(const uint8_t *text, const unsigned long long *tile_prefix, unsigned long long nl_before, int n_lines,
                                unsigned long long pod_start, unsigned long long pod_eff_end, long long *out, int num_sms, cudaStream_t s);

@@ -127,6 +127,85 @@ size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
 }  // namespace
 
+void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mode, const GramCostFn *cost, FilterBuild &out) {
+    out = FilterBuild();
+    struct Chosen {
+        int pattern;
+        const Literal *lit;
+        size_t o;
+    };
+    std::vector<Chosen> chosen;
+    bool fold = fold_mode == 1;
+    for (size_t i = 0; i < literals.size(); i++)
+        for (auto &l : literals[i]) {
+            size_t best_o = 0;
+            double best = 1e300;
+            for (size_t o = 0; o + kMinLiteral <= l.bytes.size(); o++) {
+                bool masked = false;
+                for (size_t j = o; j < o + kMinLiteral; j++) masked |= l.mask[j] != 0;
+                double c;
+                if (cost) {
+                    c = 1e-12 * window_cost(l, o);   // static model only breaks ties
+                    for (int k = 0; k < 4; k++) c += (*cost)(gram_at(l, o + k, fold_mode == 1));
+                    if (masked && fold_mode == 0) c = 1e299;   // would need fold mode, which is fixed
+                } else {
+                    c = window_cost(l, o);   // penalises masked windows (they force fold mode)
+                    if (masked && fold_mode == 0) c = 1e299;
+                }
+                if (c < best) best = c, best_o = o;
+            }
+            for (size_t j = best_o; j < best_o + kMinLiteral; j++)
+                if (l.mask[j]) fold = true;
+            chosen.push_back({(int)i, &l, best_o});
+        }
+    out.fold = fold;
+    std::map<uint32_t, std::vector<Probe>> by_gram;
+    for (auto &c : chosen) {
+        uint32_t lit_off = (uint32_t)out.litpool.size();
+        out.litpool.insert(out.litpool.end(), c.lit->bytes.begin(), c.lit->bytes.end());
+        out.litpool.insert(out.litpool.end(), c.lit->mask.begin(), c.lit->mask.end());
+        for (int k = 0; k < 4; k++) {
+            Probe pr;
+            pr.pattern = (uint32_t)c.pattern;
+            pr.lit_off = lit_off;
+            pr.lit_len = (uint16_t)c.lit->bytes.size();
+            pr.gram_off = (uint16_t)(c.o + k);
+            by_gram[gram_at(*c.lit, c.o + k, fold)].push_back(pr);
+        }
+    }
+    out.n_grams = (uint32_t)by_gram.size();
+    out.log2_bits = 0;
+    out.log2_cap = 4;
+    if (out.n_grams) {
+        out.log2_bits = 15;
+        while (out.log2_bits < 20 && (1ull << out.log2_bits) < 512ull * out.n_grams) out.log2_bits++;
+        while ((1u << out.log2_cap) < 2 * out.n_grams) out.log2_cap++;
+    }
+    out.bitmap.assign(out.log2_bits ? (1u << out.log2_bits) / 32 : 4, 0);
+    out.gkeys.assign(1u << out.log2_cap, kGramEmpty);
+    out.gfirst.assign(1u << out.log2_cap, 0);
+    out.gcount.assign(1u << out.log2_cap, 0);
+    for (auto &kv : by_gram) {
+        uint32_t bit = gram_filter_bit(kv.first, out.log2_bits);
+        out.bitmap[bit >> 5] |= 1u << (bit & 31);
+        uint32_t slot = gram_table_slot(kv.first, out.log2_cap);
+        while (out.gkeys[slot] != kGramEmpty) slot = (slot + 1) & ((1u << out.log2_cap) - 1);
+        out.gkeys[slot] = kv.first;
+        out.gfirst[slot] = out.n_probes;
+        out.gcount[slot] = (uint32_t)kv.second.size();
+        for (auto &pr : kv.second) out.probes.push_back(pr), out.n_probes++;
+    }
+}
+
+void collect_all_grams(const std::vector<std::vector<Literal>> &literals, bool fold, std::vector<uint32_t> &grams) {
+    grams.clear();
+    for (auto &ls : literals)
+        for (auto &l : ls)
+            for (size_t o = 0; o + kGramLen <= l.bytes.size(); o++) grams.push_back(gram_at(l, o, fold));
+    std::sort(grams.begin(), grams.end());
+    grams.erase(std::unique(grams.begin(), grams.end()), grams.end());
+}
+
 int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile_report &rep) {
     memset(&rep, 0, sizeof rep);
     rep.pattern_index = rep.secondary_index = rep.regex_offset = -1;
@@ -263,60 +342,17 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
             out.patterns[i].tier = (int)pdesc[i].tier;
         }
 
-        // ---- gram selection
-        struct Chosen {
-            int pattern;
-            const Literal *lit;
-            size_t o;
-        };
-        std::vector<Chosen> chosen;
-        bool fold = false;
-        for (int i = 0; i < P; i++)
-            for (auto &l : out.literals[i]) {
-                size_t best_o = 0;
-                double best = 1e300;
-                for (size_t o = 0; o + kMinLiteral <= l.bytes.size(); o++) {
-                    double c = window_cost(l, o);
-                    if (c < best) best = c, best_o = o;
-                }
-                for (size_t j = best_o; j < best_o + kMinLiteral; j++)
-                    if (l.mask[j]) fold = true;
-                chosen.push_back({i, &l, best_o});
-            }
+        // ---- gram selection (static byte-rarity model; the runtime may re-select from measured
+        //      gram frequencies, see build_filter / pm_runtime.cu)
+        FilterBuild fb;
+        build_filter(out.literals, /*fold_mode=*/-1, nullptr, fb);
+        const bool fold = fb.fold;
+        const uint32_t n_grams = fb.n_grams, n_probes = fb.n_probes, log2_bits = fb.log2_bits, log2_cap = fb.log2_cap;
+        std::vector<uint32_t> &bitmap = fb.bitmap, &gkeys = fb.gkeys, &gfirst = fb.gfirst, &gcount = fb.gcount;
         Section litpool, probes_sec;
-        std::map<uint32_t, std::vector<Probe>> by_gram;
-        for (auto &c : chosen) {
-            uint32_t lit_off = (uint32_t)litpool.push_raw(c.lit->bytes.data(), c.lit->bytes.size());
-            litpool.push_raw(c.lit->mask.data(), c.lit->mask.size());
-            for (int k = 0; k < 4; k++) {
-                Probe pr;
-                pr.pattern = (uint32_t)c.pattern;
-                pr.lit_off = lit_off;
-                pr.lit_len = (uint16_t)c.lit->bytes.size();
-                pr.gram_off = (uint16_t)(c.o + k);
-                by_gram[gram_at(*c.lit, c.o + k, fold)].push_back(pr);
-            }
-        }
-        const uint32_t n_grams = (uint32_t)by_gram.size();
-        uint32_t log2_bits = 0, log2_cap = 4;
-        if (n_grams) {
-            log2_bits = 15;
-            while (log2_bits < 20 && (1ull << log2_bits) < 512ull * n_grams) log2_bits++;
-            while ((1u << log2_cap) < 2 * n_grams) log2_cap++;
-        }
-        std::vector<uint32_t> bitmap(log2_bits ? (1u << log2_bits) / 32 : 4, 0);
-        std::vector<uint32_t> gkeys(1u << log2_cap, kGramEmpty), gfirst(1u << log2_cap, 0), gcount(1u << log2_cap, 0);
-        uint32_t n_probes = 0;
-        for (auto &kv : by_gram) {
-            uint32_t bit = gram_filter_bit(kv.first, log2_bits);
-            bitmap[bit >> 5] |= 1u << (bit & 31);
-            uint32_t slot = gram_table_slot(kv.first, log2_cap);
-            while (gkeys[slot] != kGramEmpty) slot = (slot + 1) & ((1u << log2_cap) - 1);
-            gkeys[slot] = kv.first;
-            gfirst[slot] = n_probes;
-            gcount[slot] = (uint32_t)kv.second.size();
-            for (auto &pr : kv.second) probes_sec.push(pr), n_probes++;
-        }
+        litpool.bytes = fb.litpool;
+        probes_sec.push_raw(fb.probes.data(), fb.probes.size() * sizeof(Probe));
+        out.fold = fold;
 
         // ---- combined DFAs for tier 2
         std::vector<GroupBuild> groups;

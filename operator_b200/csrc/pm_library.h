@@ -3,6 +3,7 @@
 // PatternSyncService.validatePatterns (PatternSyncService.java:228-253), which today only
 // counts YAML files.  Host-only.
 #pragma once
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -20,12 +21,31 @@ struct PatternInfo {
     int tier = 0;
 };
 
+// The gram filter of a library (bitmap + exact gram table + probes + literal pool), built from
+// the required literals of the tier-1 patterns.  Separate from the rest of the blob because the
+// runtime rebuilds it when it has measured which grams are frequent in the actual logs.
+struct FilterBuild {
+    uint32_t log2_bits = 0, log2_cap = 4, n_grams = 0, n_probes = 0;
+    bool fold = false;
+    std::vector<uint32_t> bitmap, gkeys, gfirst, gcount;
+    std::vector<Probe> probes;
+    std::vector<uint8_t> litpool;
+};
+using GramCostFn = std::function<double(uint32_t gram)>;   // expected hits per aligned text word
+
+// fold_mode: -1 decide (fold iff a chosen window has a case-insensitive position), 0/1 fixed.
+// cost == nullptr: static byte-rarity model.
+void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mode, const GramCostFn *cost, FilterBuild &out);
+// Every distinct 4-byte gram of every literal (folded when `fold`), sorted.
+void collect_all_grams(const std::vector<std::vector<Literal>> &literals, bool fold, std::vector<uint32_t> &grams);
+
 struct CompiledLibrary {
     std::vector<uint8_t> blob;
     std::vector<PatternInfo> patterns;
     // kept for the compiler's unit tests (tests/support): the automata behind the blob
     std::vector<Dfa> unit_dfas;                      // index = unit id
     std::vector<std::vector<Literal>> literals;      // per pattern (empty for tier 2)
+    bool fold = false;
     std::vector<Dfa> group_dfas;
     std::vector<std::vector<int>> group_patterns;    // unit id in a group -> pattern index
     const BlobHeader *header() const { return reinterpret_cast<const BlobHeader *>(blob.data()); }

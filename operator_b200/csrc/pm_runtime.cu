@@ -107,17 +107,16 @@ struct Device {
 
 }  // namespace
 
-// The gram filter hashes with an odd multiplier.  Which text grams collide with the set bits is
-// a matter of luck per (library, workload): when a frequent gram of the logs collides, the
-// candidate rate jumps far above the bitmap's fill rate.  The runtime watches that rate and
-// rebuilds the bitmap with another multiplier (a perf adaptation only: results never depend on
-// it, every candidate is confirmed exactly).
-struct SeedState {
-    int tried = 0;
+// Which literal grams are frequent in benign text depends on the workload ("thre" of
+// "thread-pool" is in every Quarkus log line), and the compiler's static byte-rarity model
+// cannot know.  When the candidate rate of a scan is far above the bitmap's fill rate, the
+// runtime counts EVERY gram of every literal on a sample of the staged text (k_gram_profile),
+// re-selects each literal's 7-byte window with the measured frequencies and uploads the rebuilt
+// filter.  A perf adaptation only: every candidate is confirmed exactly, results never change.
+struct AdaptState {
     bool settled = false;
-    double best_rate = 1e300;
-    uint32_t best_mult = kFilterMult0;
-    void *dev_bitmap = nullptr;
+    int rounds = 0;
+    void *dev_filter = nullptr;     // rebuilt filter sections (one allocation)
 };
 
 struct pm_library {
@@ -125,7 +124,7 @@ struct pm_library {
     std::atomic<int> refs{1};
     std::vector<DeviceLibrary> dev;   // per context device, after publish
     std::vector<void *> dev_blobs;
-    std::vector<SeedState> seed;
+    std::vector<AdaptState> adapt;
     pm_ctx *owner = nullptr;
 };
 
@@ -148,7 +147,7 @@ void lib_unref(pm_library *l) {
             if (l->dev_blobs[d]) {
                 cudaSetDevice(l->owner->devs[d]->id);
                 cudaFree(l->dev_blobs[d]);
-                if (d < l->seed.size() && l->seed[d].dev_bitmap) cudaFree(l->seed[d].dev_bitmap);
+                if (d < l->adapt.size() && l->adapt[d].dev_filter) cudaFree(l->adapt[d].dev_filter);
             }
         delete l;
     }
@@ -362,50 +361,95 @@ int stage(pm_batch *b) {
     return PM_OK;
 }
 
-const uint32_t kSeedMults[] = {kFilterMult0, 0x85EBCA77u, 0xC2B2AE3Du, 0x27D4EB2Fu, 0x165667B1u, 0xD3A2646Du, 0xFD7046C5u, 0xB55A4F09u};
-
 // Called with the device idle (stream synchronised, device mutex held by the batch).
-int maybe_reseed(pm_library *l, int slot, uint64_t n_cand, uint64_t total_bytes) {
-    const BlobHeader &h = *l->lib.header();
-    if (!h.filter_log2_bits || slot >= (int)l->seed.size()) return PM_OK;
-    SeedState &st = l->seed[slot];
-    if (st.settled || total_bytes < (8u << 20)) return PM_OK;   // small batches say nothing about rates
+int maybe_adapt(pm_library *l, DevWork &w) {
+    const int slot = w.slot;
+    if (slot >= (int)l->adapt.size()) return PM_OK;
+    AdaptState &st = l->adapt[slot];
     DeviceLibrary &dl = l->dev[slot];
-    const double words = (double)total_bytes / 4.0;
-    const double fill = (double)h.n_grams / (double)(1ull << h.filter_log2_bits);
-    const double rate = (double)n_cand / words;
-    if (rate < st.best_rate) st.best_rate = rate, st.best_mult = dl.mult;
-    if (getenv("PM_DEBUG"))
-        fprintf(stderr, "[pm] filter mult %08x: %llu candidates, rate %.5f (fill %.5f), tried %d\n", dl.mult, (unsigned long long)n_cand, rate, fill, st.tried);
-    const int n_mults = (int)(sizeof(kSeedMults) / sizeof(kSeedMults[0]));
-    uint32_t next;
-    if (rate <= 3.0 * fill + 2e-5) {
+    if (st.settled || !dl.fv.log2_bits || w.total < (8u << 20)) return PM_OK;   // small batches say nothing about rates
+    const double words = (double)w.total / 4.0;
+    const double fill = (double)dl.fv.n_grams / (double)(1ull << dl.fv.log2_bits);
+    const double rate = (double)w.n_cand / words;
+    const bool debug = getenv("PM_DEBUG") != nullptr;
+    if (debug) fprintf(stderr, "[pm] filter: %llu candidates, rate %.5f, fill %.5f, round %d\n", (unsigned long long)w.n_cand, rate, fill, st.rounds);
+    if (rate <= 3.0 * fill + 2e-5 || st.rounds >= 2) {
         st.settled = true;
         return PM_OK;
     }
-    st.tried++;
-    if (st.tried < n_mults) {
-        next = kSeedMults[st.tried];
-    } else {
-        next = st.best_mult;
-        st.settled = true;
-        if (next == dl.mult) return PM_OK;
+    st.rounds++;
+    // ---- 1. count every literal gram on a sample of the staged text
+    const bool fold = dl.fv.fold != 0;
+    std::vector<uint32_t> grams;
+    collect_all_grams(l->lib.literals, fold, grams);
+    uint32_t log2_cap = 4;
+    while ((1ull << log2_cap) < 2ull * grams.size()) log2_cap++;
+    const size_t cap = (size_t)1 << log2_cap;
+    std::vector<uint32_t> keys(cap, kGramEmpty);
+    for (uint32_t g : grams) {
+        uint32_t sl = gram_table_slot(g, log2_cap);
+        while (keys[sl] != kGramEmpty) sl = (sl + 1) & (uint32_t)(cap - 1);
+        keys[sl] = g;
     }
-    // rebuild the bitmap from the gram table with the new multiplier
-    const uint8_t *blob = l->lib.blob.data();
-    const uint32_t *gk = reinterpret_cast<const uint32_t *>(blob + h.off_gram_keys);
-    const size_t nwords = (size_t)(1u << h.filter_log2_bits) / 32;
-    std::vector<uint32_t> bm(nwords, 0);
-    for (uint32_t i = 0; i < (1u << h.gram_log2_cap); i++)
-        if (gk[i] != kGramEmpty) {
-            uint32_t bit = gram_filter_bit(gk[i], h.filter_log2_bits, next);
-            bm[bit >> 5] |= 1u << (bit & 31);
-        }
-    CU(cudaSetDevice(l->owner->devs[slot]->id));
-    if (!st.dev_bitmap) CU(cudaMalloc(&st.dev_bitmap, nwords * 4));
-    CU(cudaMemcpy(st.dev_bitmap, bm.data(), nwords * 4, cudaMemcpyHostToDevice));
-    dl.bitmap = reinterpret_cast<const uint8_t *>(st.dev_bitmap);
-    dl.mult = next;
+    Device *d = l->owner->devs[slot];
+    CU(cudaSetDevice(d->id));
+    void *dkeys = nullptr, *dcounts = nullptr;
+    CU(cudaMalloc(&dkeys, cap * 4));
+    CU(cudaMalloc(&dcounts, cap * 4));
+    CU(cudaMemcpyAsync(dkeys, keys.data(), cap * 4, cudaMemcpyHostToDevice, w.stream));
+    CU(cudaMemsetAsync(dcounts, 0, cap * 4, w.stream));
+    const unsigned long long sample = std::min<unsigned long long>(w.total, 256ull << 20) & ~15ull;
+    CU(launch_gram_profile(w.text.as<uint8_t>(), sample, reinterpret_cast<const uint32_t *>(dkeys), log2_cap, fold, reinterpret_cast<unsigned int *>(dcounts),
+                           d->num_sms, w.stream));
+    std::vector<uint32_t> counts(cap);
+    CU(cudaMemcpyAsync(counts.data(), dcounts, cap * 4, cudaMemcpyDeviceToHost, w.stream));
+    CU(cudaStreamSynchronize(w.stream));
+    cudaFree(dkeys);
+    cudaFree(dcounts);
+    // ---- 2. re-select windows with measured frequencies
+    const double sample_words = (double)sample / 4.0;
+    GramCostFn cost = [&](uint32_t g) -> double {
+        uint32_t sl = gram_table_slot(g, log2_cap);
+        while (keys[sl] != g && keys[sl] != kGramEmpty) sl = (sl + 1) & (uint32_t)(cap - 1);
+        double c = keys[sl] == g ? (double)counts[sl] : 0.0;
+        return (c + 0.25) / sample_words;
+    };
+    FilterBuild fb;
+    build_filter(l->lib.literals, fold ? 1 : 0, &cost, fb);
+    // ---- 3. upload the rebuilt sections and switch the view
+    auto a16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+    size_t o_bm = 0, o_k = a16(o_bm + fb.bitmap.size() * 4), o_f = a16(o_k + fb.gkeys.size() * 4), o_c = a16(o_f + fb.gfirst.size() * 4);
+    size_t o_p = a16(o_c + fb.gcount.size() * 4), o_l = a16(o_p + fb.probes.size() * sizeof(Probe)), total = a16(o_l + fb.litpool.size()) + 16;
+    std::vector<uint8_t> host(total, 0);
+    memcpy(host.data() + o_bm, fb.bitmap.data(), fb.bitmap.size() * 4);
+    memcpy(host.data() + o_k, fb.gkeys.data(), fb.gkeys.size() * 4);
+    memcpy(host.data() + o_f, fb.gfirst.data(), fb.gfirst.size() * 4);
+    memcpy(host.data() + o_c, fb.gcount.data(), fb.gcount.size() * 4);
+    memcpy(host.data() + o_p, fb.probes.data(), fb.probes.size() * sizeof(Probe));
+    if (!fb.litpool.empty()) memcpy(host.data() + o_l, fb.litpool.data(), fb.litpool.size());
+    void *dev = nullptr;
+    CU(cudaMalloc(&dev, total));
+    CU(cudaMemcpy(dev, host.data(), total, cudaMemcpyHostToDevice));
+    if (st.dev_filter) cudaFree(st.dev_filter);
+    st.dev_filter = dev;
+    const uint8_t *db = reinterpret_cast<const uint8_t *>(dev);
+    FilterView &fv = dl.fv;
+    fv.bitmap = reinterpret_cast<const uint32_t *>(db + o_bm);
+    fv.gkeys = reinterpret_cast<const uint32_t *>(db + o_k);
+    fv.gfirst = reinterpret_cast<const uint32_t *>(db + o_f);
+    fv.gcount = reinterpret_cast<const uint32_t *>(db + o_c);
+    fv.probes = reinterpret_cast<const Probe *>(db + o_p);
+    fv.litpool = db + o_l;
+    fv.log2_bits = fb.log2_bits;
+    fv.log2_cap = fb.log2_cap;
+    fv.n_grams = fb.n_grams;
+    if (debug) {
+        double expect = 0;
+        for (uint32_t i = 0; i < fb.gkeys.size(); i++)
+            if (fb.gkeys[i] != kGramEmpty) expect += cost(fb.gkeys[i]);
+        fprintf(stderr, "[pm] filter rebuilt from %zu profiled grams: %u grams, 2^%u bits, expected true-gram rate %.6f\n", grams.size(), fb.n_grams,
+                fb.log2_bits, expect);
+    }
     return PM_OK;
 }
 
@@ -425,7 +469,7 @@ int scan_async(pm_batch *b) {
         CU(launch_pods(w.text.as<uint8_t>(), w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), np, w.stream));
         CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.raw.as<unsigned long long>(),
                           w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
-        w.launches += 1 + 3 + (np ? 1 : 0) + (dl.h.filter_log2_bits ? 1 : 0);
+        w.launches += 1 + 3 + (np ? 1 : 0) + (dl.fv.log2_bits ? 1 : 0);
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
             CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, w.table(), (int)g, w.raw.as<unsigned long long>(), w.raw_cap,
                                w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
@@ -568,7 +612,7 @@ int finish(pm_batch *b, pm_result_view *out) {
         ms_post = std::max<double>(ms_post, p1 + p2);
         ms_d2h = std::max<double>(ms_d2h, dd);
         w.scanned = true;
-        int rs = maybe_reseed(b->lib, w.slot, w.n_cand, w.total);
+        int rs = maybe_adapt(b->lib, w);
         if (rs) return rs;
     }
     const size_t np = b->pods.size();
@@ -751,15 +795,26 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
         l->owner = ctx;
         l->dev.resize(ctx->devs.size());
         l->dev_blobs.assign(ctx->devs.size(), nullptr);
-        l->seed.assign(ctx->devs.size(), SeedState());
+        l->adapt.assign(ctx->devs.size(), AdaptState());
         for (size_t d = 0; d < ctx->devs.size(); d++) {
             CU(cudaSetDevice(ctx->devs[d]->id));
             CU(cudaMalloc(&l->dev_blobs[d], l->lib.blob.size()));
             CU(cudaMemcpy(l->dev_blobs[d], l->lib.blob.data(), l->lib.blob.size(), cudaMemcpyHostToDevice));
             l->dev[d].blob = reinterpret_cast<const uint8_t *>(l->dev_blobs[d]);
             l->dev[d].h = *l->lib.header();
-            l->dev[d].bitmap = l->dev[d].blob + l->lib.header()->off_bitmap;
-            l->dev[d].mult = kFilterMult0;
+            const BlobHeader &bh = *l->lib.header();
+            FilterView &fv = l->dev[d].fv;
+            const uint8_t *db = l->dev[d].blob;
+            fv.bitmap = reinterpret_cast<const uint32_t *>(db + bh.off_bitmap);
+            fv.gkeys = reinterpret_cast<const uint32_t *>(db + bh.off_gram_keys);
+            fv.gfirst = reinterpret_cast<const uint32_t *>(db + bh.off_gram_first);
+            fv.gcount = reinterpret_cast<const uint32_t *>(db + bh.off_gram_count);
+            fv.probes = reinterpret_cast<const Probe *>(db + bh.off_probes);
+            fv.litpool = db + bh.off_litpool;
+            fv.log2_bits = bh.filter_log2_bits;
+            fv.log2_cap = bh.gram_log2_cap;
+            fv.fold = bh.filter_fold;
+            fv.n_grams = bh.n_grams;
         }
     }
     pm_library *old;
