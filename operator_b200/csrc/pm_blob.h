@@ -24,7 +24,7 @@
 namespace pm {
 
 constexpr uint32_t kBlobMagic = 0x424C4D50u;   // "PMLB"
-constexpr uint32_t kBlobVersion = 3;
+constexpr uint32_t kBlobVersion = 4;
 constexpr int kGramLen = 4;        // bytes per gram = one aligned 32-bit text word
 constexpr int kMinLiteral = 7;     // any 7-byte window covers one aligned 4-byte word
 constexpr uint32_t kGramEmpty = 0xFFFFFFFFu;   // 0xFF never occurs in valid UTF-8
@@ -53,7 +53,10 @@ struct Probe {
 struct UnitDesc {
     uint32_t table_off;      // in u16 elements from off_tables
     uint32_t classmap_off;   // in bytes from off_classmaps
-    uint16_t nstates, stride, accept_state, pad;
+    uint16_t nstates, stride, accept_state;
+    uint16_t mid_state;      // state after one byte that belongs to no pattern (speculative walk entry guess)
+    uint16_t dead_state;     // state from which acceptance is unreachable, 0xFFFF if none (anchored regexes)
+    uint16_t pad;
 };
 
 struct PatternDesc {

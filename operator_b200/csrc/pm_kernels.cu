@@ -243,7 +243,7 @@ __device__ unsigned long long warp_newlines_before(const uint8_t *text, const un
 struct UnitTables {
     const uint16_t *tab;
     const uint8_t *cmap;
-    uint32_t stride, accept;
+    uint32_t stride, accept, dead, mid;
 };
 
 __device__ __forceinline__ UnitTables unit_tables(const uint8_t *blob, const BlobHeader &h, uint32_t unit) {
@@ -253,6 +253,8 @@ __device__ __forceinline__ UnitTables unit_tables(const uint8_t *blob, const Blo
     t.cmap = blob + h.off_classmaps + u->classmap_off;
     t.stride = u->stride;
     t.accept = u->accept_state;
+    t.dead = u->dead_state;
+    t.mid = u->mid_state;
     return t;
 }
 
@@ -262,6 +264,7 @@ __device__ bool line_matches(const uint8_t *text, unsigned long long a, unsigned
     for (unsigned long long p = a; p < b; p++) {
         s = t.tab[s * t.stride + t.cmap[text[p]]];
         if (s == t.accept) return true;
+        if (s == t.dead) return false;   // anchored regexes give up after a few bytes
     }
     s = t.tab[s * t.stride + t.stride - 1];
     return s == t.accept;
@@ -446,6 +449,54 @@ __global__ void k_mark_unique(const unsigned long long *sorted, unsigned long lo
     if (i < n) flags[i] = (sorted[i] != ~0ull) && (i == 0 || sorted[i] != sorted[i - 1]);
 }
 
+// Whole ordering step in one CTA when the batch produced few raw events (the normal case: hits
+// are ~1e-3 of lines): bitonic sort of <= kSmallSort keys in shared memory, duplicate removal,
+// count.  Reads its size from the device counters, so the host does not have to learn the event
+// count before it can enqueue the rest of the pipeline.
+__global__ void __launch_bounds__(1024, 1) k_sort_small(const unsigned long long *__restrict__ raw, const ScanCounters *ctr, unsigned long long raw_cap,
+                                                        unsigned long long *__restrict__ uniq, unsigned long long *n_unique, unsigned int *big_flag) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned long long *keys = reinterpret_cast<unsigned long long *>(smem_raw);
+    const unsigned long long n = ctr->n_raw;
+    if (ctr->cand_overflow || ctr->raw_overflow || n > (unsigned long long)kSmallSort || n > raw_cap) {
+        if (threadIdx.x == 0) {
+            *n_unique = 0;
+            *big_flag = 1;
+        }
+        return;
+    }
+    unsigned m = 1024;
+    while (m < n) m <<= 1;
+    for (unsigned i = threadIdx.x; i < m; i += blockDim.x) keys[i] = i < n ? raw[i] : ~0ull;
+    __syncthreads();
+    for (unsigned k = 2; k <= m; k <<= 1)
+        for (unsigned j = k >> 1; j > 0; j >>= 1) {
+            for (unsigned t = threadIdx.x; t < m / 2; t += blockDim.x) {
+                unsigned i = 2 * t - (t & (j - 1));   // index with bit j clear
+                unsigned l = i | j;
+                unsigned long long a = keys[i], b = keys[l];
+                bool up = (i & k) == 0;
+                if ((a > b) == up) {
+                    keys[i] = b;
+                    keys[l] = a;
+                }
+            }
+            __syncthreads();
+        }
+    // unique: each thread owns m/1024 consecutive keys
+    const unsigned per = m / 1024, i0 = threadIdx.x * per;
+    unsigned cnt = 0;
+    for (unsigned i = i0; i < i0 + per; i++) cnt += (keys[i] != ~0ull) && (i == 0 || keys[i] != keys[i - 1]);
+    __shared__ unsigned long long tot;
+    unsigned long long at = block_exclusive_scan(cnt, &tot);
+    for (unsigned i = i0; i < i0 + per; i++)
+        if ((keys[i] != ~0ull) && (i == 0 || keys[i] != keys[i - 1])) uniq[at++] = keys[i];
+    if (threadIdx.x == 0) {
+        *n_unique = tot;
+        *big_flag = 0;
+    }
+}
+
 // ------------------------------------------------------------------------------------ resolve (a12 + a13)
 // Three kernels, so that the expensive part -- walking context lines through the STACK and
 // secondary-pattern DFAs -- is balanced over the whole GPU instead of serialised per event:
@@ -535,7 +586,8 @@ __device__ void warp_collect_backward(const uint8_t *text, unsigned long long be
 
 __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
                                                           const unsigned long long *__restrict__ tile_prefix, PodTable pt,
-                                                          const unsigned long long *__restrict__ uniq, unsigned long long n_events, EventOut out,
+                                                          const unsigned long long *__restrict__ uniq, const unsigned long long *n_events_ptr,
+                                                          unsigned long long ev_cap, EventOut out,
                                                           Item *__restrict__ items, unsigned long long item_cap, uint32_t *__restrict__ long_list,
                                                           unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr) {
     __shared__ unsigned long long fwd_s[kPlanWarps][kCtxSlots];   // fwd[i]: '\n' that ends line L+i
@@ -545,6 +597,11 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
     const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
     const PodDev *pods = pt.pods;
+    const unsigned long long n_events = *n_events_ptr;
+    if (n_events > ev_cap) {
+        if (threadIdx.x == 0 && blockIdx.x == 0) ctr->overflow = 1;
+        return;
+    }
 
     for (unsigned long long ev = (unsigned long long)blockIdx.x * kPlanWarps + warp; ev < n_events; ev += (unsigned long long)gridDim.x * kPlanWarps) {
         const unsigned long long key = uniq[ev], ls = key >> kPatternBits;
@@ -681,14 +738,13 @@ __global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ 
     for (unsigned long long k = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < n; k += n_warps) {
         const uint32_t idx = long_list[k];
         const Item it = items[idx];
-        const UnitDesc *ud = reinterpret_cast<const UnitDesc *>(blob + h.off_units) + it.unit;
         UnitTables ut = unit_tables(blob, h, it.unit);
-        const uint32_t mid = ud->pad;   // mid-line idle state (pm_library.cc)
+        const uint32_t mid = ut.mid;   // mid-line idle state (pm_library.cc)
         const unsigned long long a = it.a, b = it.a + it.len;
         const unsigned long long c = (it.len + 31) / 32;
         const unsigned long long ca = min(b, a + lane * c), cb = min(b, ca + c);
         auto walk = [&](uint32_t s, unsigned long long p0, unsigned long long p1) {
-            for (unsigned long long p = p0; p < p1 && s != ut.accept; p++) s = ut.tab[s * ut.stride + ut.cmap[text[p]]];
+            for (unsigned long long p = p0; p < p1 && s != ut.accept && s != ut.dead; p++) s = ut.tab[s * ut.stride + ut.cmap[text[p]]];
             return s;
         };
         uint32_t in_spec;
@@ -707,7 +763,7 @@ __global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ 
                 out_i = __shfl_sync(FULL, redo, i);
             }
             truth = out_i;
-            if (truth == ut.accept) break;
+            if (truth == ut.accept || truth == ut.dead) break;
         }
         if (truth != ut.accept) truth = ut.tab[truth * ut.stride + ut.stride - 1];
         if (lane == 0) results[idx] = (truth == ut.accept);
@@ -715,10 +771,11 @@ __global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ 
 }
 
 __global__ void __launch_bounds__(128) k_finalize(const uint8_t *__restrict__ blob, BlobHeader h, const unsigned long long *__restrict__ uniq,
-                                                  unsigned long long n_events, EventOut out, const Item *__restrict__ items,
+                                                  const unsigned long long *n_events_ptr, EventOut out, const Item *__restrict__ items,
                                                   const unsigned char *__restrict__ results, const EvAux *__restrict__ aux, const PodTable pt,
                                                   const ResolveCounters *ctr) {
     if (ctr->overflow) return;
+    const unsigned long long n_events = *n_events_ptr;
     const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
     for (unsigned long long ev = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; ev < n_events; ev += (unsigned long long)gridDim.x * blockDim.x) {
@@ -903,20 +960,30 @@ size_t resolve_item_bytes() { return sizeof(Item); }
 size_t resolve_aux_bytes() { return sizeof(EvAux); }
 
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
-                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, const ResolveScratch &rs, int num_sms,
-                           cudaStream_t s) {
-    if (n_events == 0) return cudaSuccess;
+                           const unsigned long long *uniq, const unsigned long long *n_events_dev, unsigned long long ev_cap, EventOut out,
+                           const ResolveScratch &rs, int num_sms, cudaStream_t s) {
+    if (ev_cap == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(rs.ctr, 0, sizeof(ResolveCounters), s);
     if (e != cudaSuccess) return e;
-    unsigned blocks = (unsigned)((n_events + kPlanWarps - 1) / kPlanWarps);
+    unsigned blocks = (unsigned)((ev_cap + kPlanWarps - 1) / kPlanWarps);
     if (blocks > (unsigned)num_sms * 16u) blocks = (unsigned)num_sms * 16u;
     Item *items = reinterpret_cast<Item *>(rs.items);
-    k_plan<<<blocks, kPlanWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events, out, items, rs.item_cap, rs.long_list, rs.long_cap,
-                                              reinterpret_cast<EvAux *>(rs.aux), rs.ctr);
+    k_plan<<<blocks, kPlanWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events_dev, ev_cap, out, items, rs.item_cap, rs.long_list,
+                                              rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr);
     k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
     k_check_long<<<num_sms * 8, 128, 0, s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
-    unsigned fb = (unsigned)((n_events + 127) / 128);
-    k_finalize<<<fb, 128, 0, s>>>(lib.blob, lib.h, uniq, n_events, out, items, rs.results, reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);
+    unsigned fb = (unsigned)((ev_cap + 127) / 128);
+    if (fb > (unsigned)num_sms * 8u) fb = (unsigned)num_sms * 8u;
+    k_finalize<<<fb, 128, 0, s>>>(lib.blob, lib.h, uniq, n_events_dev, out, items, rs.results, reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *uniq,
+                              unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s) {
+    size_t smem = (size_t)kSmallSort * 8;
+    cudaError_t e = cudaFuncSetAttribute(k_sort_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_sort_small<<<1, 1024, smem, s>>>(raw, ctr, raw_cap, uniq, n_unique, big_flag);
     return cudaGetLastError();
 }
 

@@ -106,9 +106,15 @@ size_t resolve_item_bytes();
 size_t resolve_aux_bytes();
 // Four launches (k_plan, k_check, k_check_long, k_finalize).  If rs.ctr->overflow is set afterwards the
 // scratch was too small and the outputs are incomplete: call again with larger capacities.
+// n_events is read from device memory (*n_events_dev <= ev_cap, else rs.ctr->overflow is set).
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
-                           const unsigned long long *uniq, unsigned long long n_events, EventOut out, const ResolveScratch &rs, int num_sms,
-                           cudaStream_t s);
+                           const unsigned long long *uniq, const unsigned long long *n_events_dev, unsigned long long ev_cap, EventOut out,
+                           const ResolveScratch &rs, int num_sms, cudaStream_t s);
+// Ordering + de-duplication in one CTA for ctr->n_raw <= kSmallSort (otherwise *big_flag = 1 and
+// the caller falls back to launch_sort_unique once it knows the count).
+constexpr int kSmallSort = 16384;
+cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *uniq,
+                              unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s);
 // Gram profile: counts, for every aligned word of text[0, sample_bytes), the occurrences of the
 // keys of an open-addressing table (keys: 2^log2_cap u32, kGramEmpty = free; counts zeroed by the
 // caller).  Used once per library to learn which literal grams are frequent in the real logs.

@@ -374,7 +374,27 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
             u.accept_state = (uint16_t)d.first_accept;   // early-accept: one sticky state
             // mid-line idle state: where the DFA sits after one byte that belongs to no pattern;
             // the entry-state guess of the speculative long-line walk (k_check_long)
-            u.pad = d.next[(size_t)d.classmap[0x01]];
+            u.mid_state = d.next[(size_t)d.classmap[0x01]];
+            {   // dead state: cannot reach the accepting state (backward reachability on the minimised DFA,
+                // where all such states have been merged into one)
+                const int ns = d.nstates, st = d.stride();
+                std::vector<char> live(ns, 0);
+                for (int q = d.first_accept; q < ns; q++) live[q] = 1;
+                for (bool changed = true; changed;) {
+                    changed = false;
+                    for (int q = 0; q < ns; q++)
+                        if (!live[q])
+                            for (int c = 0; c < st; c++)
+                                if (live[d.next[(size_t)q * st + c]]) {
+                                    live[q] = 1;
+                                    changed = true;
+                                    break;
+                                }
+                }
+                u.dead_state = 0xFFFF;
+                for (int q = 0; q < ns; q++)
+                    if (!live[q]) u.dead_state = (uint16_t)q;
+            }
             if (d.first_accept >= d.nstates)
                 throw CompileFail{PM_E_UNSUPPORTED, -1, -1, -1, "", "regex can never match"};
             units_sec.push(u);

@@ -168,7 +168,7 @@ struct DevWork {
     uint64_t cand_cap = 0, raw_cap = 0;
     Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, ev_soa, lines_tmp;
     Buf rs_items, rs_results, rs_long, rs_aux, rs_ctr, h_rs_ctr;   // resolve-stage scratch
-    uint64_t item_cap = 0, long_cap = 0;
+    uint64_t item_cap = 0, long_cap = 0, ev_cap = 0;
     int any_trailing_cr = 0;
     PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
@@ -346,6 +346,7 @@ int stage(pm_batch *b) {
         if ((rc = get(d->pool, sizeof(ScanCounters) + 64, w.ctr))) return rc;
         if ((rc = get(d->pool, sizeof(PodDev) * (np + 1), w.pods_dev))) return rc;
         if ((rc = get(ctx->pinned, sizeof(ScanCounters) + 64, w.h_ctr))) return rc;
+        memset(w.h_ctr.p, 0, sizeof(ScanCounters) + 64);
         CU(cudaMemcpyAsync(w.pods_dev.p, hp, sizeof(PodDev) * np, cudaMemcpyHostToDevice, w.stream));
         CU(cudaEventRecord(w.e[0], w.stream));
         for (int k = 0; k < np; k++) {
@@ -453,6 +454,55 @@ int maybe_adapt(pm_library *l, DevWork &w) {
     return PM_OK;
 }
 
+// Device-side layout of the small counters block `w.ctr`: ScanCounters, then the unique-event
+// count (u64) and the "too many raw events for the one-CTA sort" flag (u32).
+constexpr size_t kOffUnique = sizeof(ScanCounters);
+constexpr size_t kOffBig = sizeof(ScanCounters) + 8;
+constexpr size_t kCtrBytes = sizeof(ScanCounters) + 16;
+
+// Scratch of the resolve stage for up to ev_cap events (grow-only).
+int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
+    pm_ctx *ctx = b->ctx;
+    Device *d = ctx->devs[w.slot];
+    if (ev_cap < w.ev_cap) ev_cap = w.ev_cap;
+    w.ev_cap = ev_cap;
+    w.item_cap = std::min<uint64_t>(std::max<uint64_t>(w.item_cap, ev_cap * 96 + (1u << 16)), 0xFFFFFFF0ull);
+    w.long_cap = std::max<uint64_t>(w.long_cap, w.item_cap / 8 + (1u << 12));
+    SoaLayout L(ev_cap);
+    int rc;
+    if ((rc = get(d->pool, L.bytes, w.ev_soa))) return rc;
+    if ((rc = get(ctx->pinned, L.bytes, w.h_soa))) return rc;
+    if ((rc = get(d->pool, w.item_cap * resolve_item_bytes(), w.rs_items))) return rc;
+    if ((rc = get(d->pool, w.item_cap, w.rs_results))) return rc;
+    if ((rc = get(d->pool, w.long_cap * 4, w.rs_long))) return rc;
+    if ((rc = get(d->pool, ev_cap * resolve_aux_bytes(), w.rs_aux))) return rc;
+    if ((rc = get(d->pool, sizeof(ResolveCounters), w.rs_ctr))) return rc;
+    if ((rc = get(ctx->pinned, sizeof(ResolveCounters), w.h_rs_ctr))) return rc;
+    if ((rc = get(d->pool, ev_cap * 8 + 64, w.uniq))) return rc;
+    return PM_OK;
+}
+
+// Enqueues the resolve stage and the result copies; the event count is read on the device.
+int enqueue_resolve(pm_batch *b, DevWork &w) {
+    Device *d = b->ctx->devs[w.slot];
+    const DeviceLibrary &dl = b->lib->dev[w.slot];
+    SoaLayout L(w.ev_cap);
+    ResolveScratch rs{w.rs_items.p, w.item_cap, w.rs_results.as<unsigned char>(), w.rs_long.as<uint32_t>(), w.long_cap, w.rs_aux.p,
+                      w.rs_ctr.as<ResolveCounters>()};
+    const unsigned long long *n_unique = reinterpret_cast<const unsigned long long *>(w.ctr.as<char>() + kOffUnique);
+    CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), w.uniq.as<unsigned long long>(), n_unique, w.ev_cap,
+                      L.on(w.ev_soa.p), rs, d->num_sms, w.stream));
+    w.launches += 4;
+    CU(cudaEventRecord(w.e[6], w.stream));
+    CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
+    CU(cudaMemcpyAsync(w.h_rs_ctr.p, w.rs_ctr.p, sizeof(ResolveCounters), cudaMemcpyDeviceToHost, w.stream));
+    CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, kCtrBytes, cudaMemcpyDeviceToHost, w.stream));
+    CU(cudaEventRecord(w.e[7], w.stream));
+    return PM_OK;
+}
+
+// The whole pipeline of one scan, enqueued without a host round trip: scan, newline prefix,
+// pod bases, confirm (+ combined DFAs), one-CTA sort/unique, resolve, result copies.
 int scan_async(pm_batch *b) {
     pm_ctx *ctx = b->ctx;
     for (auto &w : b->work) {
@@ -460,7 +510,9 @@ int scan_async(pm_batch *b) {
         CU(cudaSetDevice(d->id));
         const DeviceLibrary &dl = b->lib->dev[w.slot];
         const int np = (int)w.pods.size();
-        CU(cudaMemsetAsync(w.ctr.p, 0, sizeof(ScanCounters), w.stream));
+        int rc = ensure_resolve_scratch(b, w, kSmallSort);
+        if (rc) return rc;
+        CU(cudaMemsetAsync(w.ctr.p, 0, kCtrBytes, w.stream));
         CU(cudaEventRecord(w.e[2], w.stream));
         CU(launch_scan(w.text.as<uint8_t>(), w.n_tiles, dl, w.tile_nl.as<uint32_t>(), w.cand.as<unsigned long long>(), w.cand_cap,
                        w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
@@ -475,16 +527,21 @@ int scan_async(pm_batch *b) {
                                w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
             w.launches++;
         }
-        CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, sizeof(ScanCounters), cudaMemcpyDeviceToHost, w.stream));
+        CU(launch_sort_small(w.raw.as<unsigned long long>(), w.ctr.as<ScanCounters>(), w.raw_cap, w.uniq.as<unsigned long long>(),
+                             reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
+                             reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream));
+        w.launches++;
         CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream));
         CU(cudaEventRecord(w.e[4], w.stream));
+        CU(cudaEventRecord(w.e[5], w.stream));
+        if ((rc = enqueue_resolve(b, w))) return rc;
     }
     return PM_OK;
 }
 
 int finish(pm_batch *b, pm_result_view *out) {
     pm_ctx *ctx = b->ctx;
-    // ---- phase 1: candidate/raw counts are known -> order, de-duplicate, resolve
+    // ---- phase 1: wait; rerun with larger queues if the candidate / raw-event queues overflowed
     for (;;) {
         bool again = false;
         for (auto &w : b->work) {
@@ -506,85 +563,43 @@ int finish(pm_batch *b, pm_result_view *out) {
             }
         }
         if (!again) break;
-        int rc = scan_async(b);   // rerun with larger queues (all devices: keeps the code simple)
+        int rc = scan_async(b);   // all devices: keeps the code simple, and overflow is rare
         if (rc) return rc;
     }
+    // ---- phase 1b: batches with more raw events than the one-CTA sort takes go through the radix
+    //      sort, which needs the count on the host; a too-small work-item queue is grown and
+    //      the resolve stage repeated
     for (auto &w : b->work) {
         Device *d = ctx->devs[w.slot];
         CU(cudaSetDevice(d->id));
-        const DeviceLibrary &dl = b->lib->dev[w.slot];
         ScanCounters *c = w.h_ctr.as<ScanCounters>();
-        uint64_t n_raw = c->n_raw;
         w.n_cand = c->n_cand;
         w.n_verified = c->n_verified;
-        int rc;
-        CU(cudaEventRecord(w.e[5], w.stream));
-        if (n_raw) {
+        const bool big = *reinterpret_cast<unsigned int *>(w.h_ctr.as<char>() + kOffBig) != 0;
+        if (big) {
+            const uint64_t n_raw = c->n_raw;
+            int rc;
+            CU(cudaEventRecord(w.e[5], w.stream));
             size_t tb = sort_temp_bytes(n_raw);
             if ((rc = get(d->pool, n_raw * 8, w.sorted))) return rc;
-            if ((rc = get(d->pool, n_raw * 8 + 64, w.uniq))) return rc;
             if ((rc = get(d->pool, tb, w.temp))) return rc;
-            unsigned long long *n_unique = reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + sizeof(ScanCounters));
+            if ((rc = ensure_resolve_scratch(b, w, n_raw))) return rc;   // uniq holds up to n_raw keys
+            unsigned long long *n_unique = reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique);
             CU(launch_sort_unique(w.raw.as<unsigned long long>(), w.sorted.as<unsigned long long>(), w.uniq.as<unsigned long long>(), n_raw, n_unique,
                                   w.temp.p, tb, w.stream));
             w.launches += 1;
-            CU(cudaMemcpyAsync(w.h_ctr.as<char>() + sizeof(ScanCounters), n_unique, 8, cudaMemcpyDeviceToHost, w.stream));
-        } else {
-            *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + sizeof(ScanCounters)) = 0;
-        }
-        (void)dl;
-    }
-    // resolve stage: sized from the event count; reruns with larger scratch if the work-item
-    // queue overflowed (the flag is read together with the results)
-    auto launch_resolve_for = [&](DevWork &w) -> int {
-        Device *d = ctx->devs[w.slot];
-        CU(cudaSetDevice(d->id));
-        const DeviceLibrary &dl = b->lib->dev[w.slot];
-        int rc;
-        if (w.n_events) {
-            SoaLayout L(w.n_events);
-            if (!w.item_cap) w.item_cap = w.n_events * 96 + (1u << 16);
-            if (!w.long_cap) w.long_cap = w.item_cap / 8 + (1u << 12);
-            w.item_cap = std::min<uint64_t>(w.item_cap, 0xFFFFFFF0ull);
-            if ((rc = get(d->pool, L.bytes, w.ev_soa))) return rc;
-            if ((rc = get(ctx->pinned, L.bytes, w.h_soa))) return rc;
-            if ((rc = get(d->pool, w.item_cap * resolve_item_bytes(), w.rs_items))) return rc;
-            if ((rc = get(d->pool, w.item_cap, w.rs_results))) return rc;
-            if ((rc = get(d->pool, w.long_cap * 4, w.rs_long))) return rc;
-            if ((rc = get(d->pool, w.n_events * resolve_aux_bytes(), w.rs_aux))) return rc;
-            if ((rc = get(d->pool, sizeof(ResolveCounters), w.rs_ctr))) return rc;
-            if ((rc = get(ctx->pinned, sizeof(ResolveCounters), w.h_rs_ctr))) return rc;
-            ResolveScratch rs{w.rs_items.p, w.item_cap, w.rs_results.as<unsigned char>(), w.rs_long.as<uint32_t>(), w.long_cap, w.rs_aux.p,
-                              w.rs_ctr.as<ResolveCounters>()};
-            CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), w.uniq.as<unsigned long long>(),
-                              w.n_events, L.on(w.ev_soa.p), rs, d->num_sms, w.stream));
-            w.launches += 4;
-            CU(cudaEventRecord(w.e[6], w.stream));
-            CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
-            CU(cudaMemcpyAsync(w.h_rs_ctr.p, w.rs_ctr.p, sizeof(ResolveCounters), cudaMemcpyDeviceToHost, w.stream));
-        } else {
-            CU(cudaEventRecord(w.e[6], w.stream));
-        }
-        CU(cudaEventRecord(w.e[7], w.stream));
-        return PM_OK;
-    };
-    for (auto &w : b->work) {
-        CU(cudaSetDevice(ctx->devs[w.slot]->id));
-        CU(cudaStreamSynchronize(w.stream));
-        w.n_events = *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + sizeof(ScanCounters));
-        int rc = launch_resolve_for(w);
-        if (rc) return rc;
-    }
-    for (auto &w : b->work) {
-        while (w.n_events) {
-            CU(cudaSetDevice(ctx->devs[w.slot]->id));
+            if ((rc = enqueue_resolve(b, w))) return rc;
             CU(cudaStreamSynchronize(w.stream));
-            if (!w.h_rs_ctr.as<ResolveCounters>()->overflow) break;
-            w.item_cap *= 4;
-            w.long_cap *= 4;
-            int rc = launch_resolve_for(w);
-            if (rc) return rc;
         }
+        while (w.h_rs_ctr.as<ResolveCounters>()->overflow) {
+            w.item_cap = std::min<uint64_t>(w.item_cap * 4, 0xFFFFFFF0ull);
+            w.long_cap *= 4;
+            int rc;
+            if ((rc = ensure_resolve_scratch(b, w, w.ev_cap))) return rc;
+            if ((rc = enqueue_resolve(b, w))) return rc;
+            CU(cudaStreamSynchronize(w.stream));
+        }
+        w.n_events = *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + kOffUnique);
     }
     // ---- phase 2: gather in batch pod order
     uint64_t total_events = 0, bytes = 0, n_cand = 0, n_ver = 0;
@@ -630,7 +645,7 @@ int finish(pm_batch *b, pm_result_view *out) {
         DevWork &w = b->work[k];
         dev_first[k].assign(w.pods.size() + 1, w.n_events);
         if (w.n_events) {
-            EventOut S = SoaLayout(w.n_events).on(w.h_soa.p);
+            EventOut S = SoaLayout(w.ev_cap).on(w.h_soa.p);
             int prev = -1;
             for (uint64_t i = 0; i < w.n_events; i++)
                 while (prev < S.pod[i]) dev_first[k][++prev] = i;
@@ -652,7 +667,7 @@ int finish(pm_batch *b, pm_result_view *out) {
         nlines[i] = nl;
         uint64_t a = dev_first[slot_index[p.dev]][p.local], e = dev_first[slot_index[p.dev]][p.local + 1];
         if (e > a) {
-            EventOut S = SoaLayout(w.n_events).on(w.h_soa.p);
+            EventOut S = SoaLayout(w.ev_cap).on(w.h_soa.p);
             size_t cnt = e - a;
             memcpy(R.line_start + at, S.line_start + a, cnt * 8);
             memcpy(R.ctx_start + at, S.ctx_start + a, cnt * 8);
