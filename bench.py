@@ -215,7 +215,7 @@ def main():
         launches += r.gpu_launches
     sync_all()
     wall_dev = time.perf_counter() - t0
-    n_events, n_cand = r.n_events, r.n_candidates
+    n_events, n_cand, n_ver = r.n_events, r.n_candidates, r.n_verified
     d2h_bytes = int(r.n_events) * 64 + 64
     b.release()
 
@@ -262,7 +262,8 @@ def main():
             "config": {"workload": "configs[1]: 1 GiB synthetic crash-log corpus vs 500-pattern library, per GPU", "corpus_bytes_per_gpu": nbytes,
                        "lines_per_gpu": n_lines, "patterns": args.patterns, "p_hit": P_HIT, "parallelism": "pod-sharded x%d, no collective" % world,
                        "l2": "input (1 GiB per GPU) is larger than the 126 MB L2; no flush between iterations",
-                       "events_per_step": int(n_events), "filter_candidates_per_step": int(n_cand)},
+                       "events_per_step": int(n_events), "filter_candidates_per_step": int(n_cand),
+                       "literal_confirms_per_step": int(n_ver)},
             "e2e": {"value": total_bytes / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": nbytes + 64, "d2h_bytes_per_step": d2h_bytes,
                     "h2d_ms_per_step": h2d_ms, "h2d_gbs": nbytes / (h2d_ms * 1e-3) / 1e9 if h2d_ms else None, "steps": e2e_steps},
             "gpu_launches": int(launches),

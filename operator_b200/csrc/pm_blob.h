@@ -24,7 +24,7 @@
 namespace pm {
 
 constexpr uint32_t kBlobMagic = 0x424C4D50u;   // "PMLB"
-constexpr uint32_t kBlobVersion = 4;
+constexpr uint32_t kBlobVersion = 5;
 constexpr int kGramLen = 4;        // bytes per gram = one aligned 32-bit text word
 constexpr int kMinLiteral = 7;     // any 7-byte window covers one aligned 4-byte word
 constexpr uint32_t kGramEmpty = 0xFFFFFFFFu;   // 0xFF never occurs in valid UTF-8
@@ -35,8 +35,10 @@ struct BlobHeader {
     uint32_t magic, version;
     uint32_t n_patterns, n_units, n_secondaries, stack_unit;
     uint32_t filter_log2_bits;   // 0: no pattern uses the gram filter
+    uint32_t filter_log2_bits2;  // second, smaller bitmap (independent hash) checked on a first-level hit
     uint32_t filter_fold;        // 1: text words are OR-ed with 0x20202020 before hashing
     uint32_t gram_log2_cap, n_grams, n_probes, n_groups;
+    uint64_t off_bitmap2;
     uint64_t off_bitmap, off_gram_keys, off_gram_first, off_gram_count, off_probes, off_litpool;
     uint64_t off_units, off_classmaps, off_tables, off_patterns, off_secondaries, off_groups;
     uint64_t off_group_accept;   // u32 pool: per-group accept index + lists
@@ -82,6 +84,7 @@ struct GroupDesc {
 
 constexpr uint32_t kFilterMult0 = 0x9E3779B1u;   // default multiplier; the runtime may reseed (pm_runtime.cu)
 PM_HD uint32_t gram_filter_bit(uint32_t gram, uint32_t log2_bits, uint32_t mult = kFilterMult0) { return (gram * mult) >> (32u - log2_bits); }
+PM_HD uint32_t gram_filter_bit2(uint32_t gram, uint32_t log2_bits2) { return (gram * 0xC2B2AE3Du) >> (32u - log2_bits2); }
 PM_HD uint32_t gram_table_slot(uint32_t gram, uint32_t log2_cap) { return (gram * 0x85EBCA6Bu) >> (32u - log2_cap); }
 
 }  // namespace pm

@@ -30,6 +30,22 @@ __device__ __forceinline__ uint4 ld_stream16(const uint4 *p) {
     return r;
 }
 
+// Streaming load that is also first in line for eviction from L2: the log text is read once,
+// while the library tables and the small index arrays are re-read by every later kernel and
+// should survive the 1 GiB stream in the 126 MB L2.
+__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint4 ld_stream16_ef(const uint4 *p, unsigned long long pol) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p), "l"(pol));
+    return r;
+}
+
 // bit 7 of every byte of the result is set iff that byte of w is NOT '\n' (exact, carry-free)
 __device__ __forceinline__ uint32_t not_newline_flags(uint32_t w) {
     uint32_t t = (w ^ 0x0A0A0A0Au) & 0x7F7F7F7Fu;
@@ -61,16 +77,20 @@ __device__ __forceinline__ uint32_t filter_word(uint32_t w, const uint32_t *bm) 
 
 template <int BITS, bool FOLD>
 __global__ void __launch_bounds__(kScanThreads, 1)
-k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g,
-       uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g, const uint4 *__restrict__ bitmap2_g,
+       uint32_t bits2, uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
        ScanCounters *__restrict__ ctr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int kBitmapWords = (1 << BITS) / 32;
     uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);
-    unsigned long long *queues = reinterpret_cast<unsigned long long *>(smem_raw + (size_t)kBitmapWords * 4);
+    const int bm2_words = (1 << bits2) / 32;
+    uint32_t *bm2 = bm + kBitmapWords;
+    unsigned long long *queues = reinterpret_cast<unsigned long long *>(smem_raw + (size_t)(kBitmapWords + bm2_words) * 4);
+    const uint32_t shift2 = 32 - bits2;
 
-    // stage the gram filter: 2^BITS bits, 128-bit copies
+    // stage the gram filter: 2^BITS bits (+ the smaller second-level bitmap), 128-bit copies
     for (int i = threadIdx.x; i < kBitmapWords / 4; i += blockDim.x) reinterpret_cast<uint4 *>(bm)[i] = bitmap_g[i];
+    for (int i = threadIdx.x; i < bm2_words / 4; i += blockDim.x) reinterpret_cast<uint4 *>(bm2)[i] = bitmap2_g[i];
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -78,12 +98,13 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
     int qn = 0;
     const unsigned long long n_warps = (unsigned long long)gridDim.x * (kScanThreads / 32);
     const unsigned lt = lanemask_lt();
+    const unsigned long long pol = l2_evict_first_policy();
 
     for (unsigned long long t = (unsigned long long)blockIdx.x * (kScanThreads / 32) + warp; t < n_tiles; t += n_warps) {
         const uint4 *base = text + t * (kTileBytes / 16) + lane;
         uint4 v[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = ld_stream16(base + j * 32);   // 4 x 512 B per warp in flight
+        for (int j = 0; j < 4; j++) v[j] = ld_stream16_ef(base + j * 32, pol);   // 4 x 512 B per warp in flight
         uint32_t nz = 0;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
@@ -93,7 +114,21 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
             uint32_t m4 = filter_word<BITS, FOLD>(v[j].x, bm) | (filter_word<BITS, FOLD>(v[j].y, bm) << 1) |
                           (filter_word<BITS, FOLD>(v[j].z, bm) << 2) | (filter_word<BITS, FOLD>(v[j].w, bm) << 3);
             unsigned b = __ballot_sync(FULL, m4 != 0);
-            if (b) {   // warp-uniform, rare: stage (group, mask) entries, flush 32 at a time
+            if (b) {   // warp-uniform, rare.  Second-level filter first: an independent hash into a small
+                       // bitmap removes the first level's collisions before anything is queued
+                if (m4) {
+                    const uint32_t w4[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+                    for (int k = 0; k < 4; k++)
+                        if (m4 & (1u << k)) {
+                            uint32_t g = FOLD ? (w4[k] | 0x20202020u) : w4[k];
+                            uint32_t bit2 = (g * 0xC2B2AE3Du) >> shift2;
+                            if (!((bm2[bit2 >> 5] >> (bit2 & 31u)) & 1u)) m4 &= ~(1u << k);
+                        }
+                }
+                b = __ballot_sync(FULL, m4 != 0);
+            }
+            if (b) {   // stage (group, mask) entries, flush 32 at a time
                 if (m4) wq[qn + __popc(b & lt)] = ((t * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
                 qn += __popc(b);
                 __syncwarp();
@@ -310,16 +345,21 @@ __global__ void k_pods(const uint8_t *text, const unsigned long long *tile_prefi
 
 // ------------------------------------------------------------------------------------ k_confirm
 __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h,
-                                                 FilterView fv, PodTable pt, const unsigned long long *__restrict__ cand, unsigned long long cand_cap,
-                                                 unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
+                                                 FilterView fv, const unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+                                                 unsigned long long *__restrict__ tasks, unsigned long long task_cap, ScanCounters *ctr) {
+    // Stage 1 of the confirmation: candidate -> exact gram -> literal.  Survivors become verify
+    // tasks (position, pattern).  One WARP per candidate: the gram lookup is uniform, then every
+    // lane takes one probe of the gram's probe list and compares its literal.  (One thread per
+    // candidate made each warp serialise 32 unrelated probe/compare loops.)
     if (ctr->cand_overflow) return;   // the host reruns the scan with a larger queue
+    const int lane = threadIdx.x & 31;
     const unsigned long long n = ctr->n_cand < cand_cap ? ctr->n_cand : cand_cap;
     const uint32_t *gk = fv.gkeys, *gf = fv.gfirst, *gc = fv.gcount;
     const Probe *probes = fv.probes;
     const uint8_t *litpool = fv.litpool;
-    const PatternDesc *pd = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const uint32_t cap_mask = (1u << fv.log2_cap) - 1u;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long n_warps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long i = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += n_warps) {
         unsigned long long e = cand[i];
         unsigned long long group = e >> 4;
         uint32_t m4 = (uint32_t)(e & 15u);
@@ -332,36 +372,122 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
             uint32_t slot = gram_table_slot(g, fv.log2_cap);
             uint32_t key;
             while ((key = gk[slot]) != g && key != kGramEmpty) slot = (slot + 1) & cap_mask;
-            if (key != g) continue;   // bitmap collision
-            for (uint32_t q = gf[slot], qe = q + gc[slot]; q < qe; q++) {
-                Probe pr = probes[q];
-                if (p < kHeaderBytes + pr.gram_off) continue;
-                unsigned long long st = p - pr.gram_off;
-                if (st + pr.lit_len > total) continue;
-                const uint8_t *lit = litpool + pr.lit_off, *msk = lit + pr.lit_len;
-                bool eq = true;
-                for (uint32_t j = 0; j < pr.lit_len; j++)
-                    if ((uint8_t)(text[st + j] | msk[j]) != lit[j]) {
-                        eq = false;
-                        break;
+            if (key != g) continue;   // filter collision (warp-uniform)
+            const uint32_t q0 = gf[slot], qn = gc[slot];
+            for (uint32_t qb = 0; qb < qn; qb += 32) {
+                const uint32_t q = qb + lane;
+                bool eq = false;
+                Probe pr;
+                if (q < qn) {
+                    pr = probes[q0 + q];
+                    if (p >= kHeaderBytes + pr.gram_off && p - pr.gram_off + pr.lit_len <= total) {
+                        const unsigned long long st = p - pr.gram_off;
+                        const uint8_t *lit = litpool + pr.lit_off, *msk = lit + pr.lit_len;
+                        eq = true;
+                        for (uint32_t j = 0; j < pr.lit_len; j++)
+                            if ((uint8_t)(text[st + j] | msk[j]) != lit[j]) {
+                                eq = false;
+                                break;
+                            }
                     }
-                if (!eq) continue;
-                atomicAdd(&ctr->n_verified, 1ull);
-                // the line that holds the gram
-                unsigned long long ls = p, le = p;
-                while (text[ls - 1] != '\n') ls--;
-                while (text[le] != '\n') le++;
-                unsigned long long lend = strip_cr(text, pt, ls, le);
-                UnitTables ut = unit_tables(blob, h, pd[pr.pattern].unit);
-                if (line_matches(text, ls, lend, ut)) {
-                    unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
-                    if (at < raw_cap)
-                        raw[at] = (ls << kPatternBits) | pr.pattern;
+                }
+                if (eq) {
+                    unsigned long long at = atomicAdd(&ctr->n_verified, 1ull);
+                    if (at < task_cap)
+                        tasks[at] = (p << kPatternBits) | pr.pattern;
                     else
                         ctr->raw_overflow = 1;
                 }
             }
         }
+    }
+}
+
+// Stage 2: one warp per verify task.  The chain "find the line, fetch the pattern's tables, walk
+// the line" is a string of dependent cache misses when one thread does it byte by byte, so the
+// warp fetches in bulk instead: 512 bytes around the literal in one round trip (newline search by
+// ballot), the pattern's class map and table into shared memory, the line into shared memory;
+// lane 0 then walks the DFA out of shared memory.
+constexpr int kVerifyWarps = 4, kVerifyTable = 8192, kVerifyLine = 1024;
+
+__global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h, PodTable pt,
+                                                              const unsigned long long *__restrict__ tasks, unsigned long long task_cap,
+                                                              unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
+    __shared__ __align__(16) uint16_t s_tab[kVerifyWarps][kVerifyTable / 2];
+    __shared__ __align__(16) uint8_t s_cmap[kVerifyWarps][256];
+    __shared__ __align__(16) uint8_t s_line[kVerifyWarps][kVerifyLine];
+    if (ctr->cand_overflow || ctr->raw_overflow) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long n = ctr->n_verified < task_cap ? ctr->n_verified : task_cap;
+    const PatternDesc *pd = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
+    const unsigned long long n_warps = (unsigned long long)gridDim.x * kVerifyWarps;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * kVerifyWarps + warp; i < n; i += n_warps) {
+        const unsigned long long t = tasks[i], p = t >> kPatternBits;
+        const uint32_t pat = (uint32_t)(t & ((1u << kPatternBits) - 1u));
+        const UnitDesc ud = reinterpret_cast<const UnitDesc *>(blob + h.off_units)[pd[pat].unit];
+        // ---- line bounds: 16 lanes look back, 16 lanes look ahead, 256 bytes each, one round trip
+        const unsigned long long p16 = p & ~15ull;
+        unsigned long long a = lane < 16 ? p16 - 16ull * (lane + 1) : p16 + 16ull * (lane - 16);
+        uint32_t m = 0;
+        if (lane >= 16 || p16 >= 16ull * (lane + 1)) m = newline_mask16(*reinterpret_cast<const uint4 *>(text + a));
+        if (lane == 16) m &= ~((1u << (p - p16)) - 1u);          // forward search starts at p
+        unsigned has = __ballot_sync(FULL, m != 0);
+        unsigned long long ls, le;
+        unsigned fwd = has >> 16, back = has & 0xFFFFu;
+        if (fwd) {
+            int src = 16 + __ffs(fwd) - 1;
+            uint32_t mm = __shfl_sync(FULL, m, src);
+            le = p16 + 16ull * (src - 16) + (__ffs(mm) - 1);
+        } else {
+            le = p16 + 256;
+            while (text[le] != '\n') le++;
+        }
+        // backward: the nearest newline strictly before p (bytes of p16's own chunk below p belong to lane 16's chunk)
+        uint32_t m_own = __shfl_sync(FULL, lane == 16 ? newline_mask16(*reinterpret_cast<const uint4 *>(text + p16)) & ((1u << (p - p16)) - 1u) : 0u, 16);
+        if (m_own) {
+            ls = p16 + (31 - __clz(m_own)) + 1;
+        } else if (back) {
+            int src = __ffs(back) - 1;                           // lane 0 is the nearest chunk
+            uint32_t mm = __shfl_sync(FULL, m, src);
+            ls = p16 - 16ull * (src + 1) + (31 - __clz(mm)) + 1;
+        } else {
+            ls = p16 >= 256 ? p16 - 256 : 0;
+            while (ls > 0 && text[ls - 1] != '\n') ls--;
+        }
+        const unsigned long long lend = strip_cr(text, pt, ls, le);
+        const unsigned long long len = lend - ls;
+        // ---- stage tables and line
+        const uint16_t *gtab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off;
+        const uint8_t *gcm = blob + h.off_classmaps + ud.classmap_off;
+        const uint32_t n_entries = (uint32_t)ud.nstates * ud.stride;
+        const bool tab_fits = n_entries * 2 <= kVerifyTable, line_fits = len <= kVerifyLine;
+        __syncwarp();
+        if (tab_fits)
+            for (uint32_t k = lane; k < n_entries; k += 32) s_tab[warp][k] = gtab[k];
+        for (int k = lane; k < 256 / 4; k += 32) reinterpret_cast<uint32_t *>(s_cmap[warp])[k] = reinterpret_cast<const uint32_t *>(gcm)[k];
+        if (line_fits)
+            for (unsigned long long k = lane; k < len; k += 32) s_line[warp][k] = text[ls + k];
+        __syncwarp();
+        if (lane == 0) {
+            const uint16_t *tab = tab_fits ? s_tab[warp] : gtab;
+            const uint8_t *cm = s_cmap[warp];
+            uint32_t st = 0;
+            const uint32_t stride = ud.stride, acc = ud.accept_state, dead = ud.dead_state;
+            if (line_fits) {
+                for (unsigned long long k = 0; k < len && st != acc && st != dead; k++) st = tab[st * stride + cm[s_line[warp][k]]];
+            } else {
+                for (unsigned long long k = ls; k < lend && st != acc && st != dead; k++) st = tab[st * stride + cm[text[k]]];
+            }
+            if (st != acc) st = tab[st * stride + stride - 1];
+            if (st == acc) {
+                unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
+                if (at < raw_cap)
+                    raw[at] = (ls << kPatternBits) | pat;
+                else
+                    ctr->raw_overflow = 1;
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -449,50 +575,94 @@ __global__ void k_mark_unique(const unsigned long long *sorted, unsigned long lo
     if (i < n) flags[i] = (sorted[i] != ~0ull) && (i == 0 || sorted[i] != sorted[i - 1]);
 }
 
-// Whole ordering step in one CTA when the batch produced few raw events (the normal case: hits
-// are ~1e-3 of lines): bitonic sort of <= kSmallSort keys in shared memory, duplicate removal,
-// count.  Reads its size from the device counters, so the host does not have to learn the event
-// count before it can enqueue the rest of the pipeline.
-__global__ void __launch_bounds__(1024, 1) k_sort_small(const unsigned long long *__restrict__ raw, const ScanCounters *ctr, unsigned long long raw_cap,
-                                                        unsigned long long *__restrict__ uniq, unsigned long long *n_unique, unsigned int *big_flag) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned long long *keys = reinterpret_cast<unsigned long long *>(smem_raw);
+// Ordering + de-duplication of the raw events when there are few of them (the normal case: hits
+// are ~1e-3 of lines; <= kSmallSort keys).  Three small launches that read their size from the
+// device counters, so the host need not learn the event count before it can enqueue the rest of
+// the pipeline:
+//   k_sort_chunks   16 CTAs, each bitonic-sorts one 1024-key chunk in shared memory
+//   k_sort_merge    every key finds its global rank by binary search in the other 15 chunks
+//   k_sort_unique   one CTA drops duplicates and counts
+constexpr int kSortChunk = 1024, kSortChunks = kSmallSort / kSortChunk;
+
+__device__ __forceinline__ bool sort_too_big(const ScanCounters *ctr, unsigned long long raw_cap) {
+    return ctr->cand_overflow || ctr->raw_overflow || ctr->n_raw > (unsigned long long)kSmallSort || ctr->n_raw > raw_cap;
+}
+
+__global__ void __launch_bounds__(kSortChunk / 2) k_sort_chunks(const unsigned long long *__restrict__ raw, const ScanCounters *ctr, unsigned long long raw_cap,
+                                                                unsigned long long *__restrict__ chunks) {
+    __shared__ unsigned long long keys[kSortChunk];
+    if (sort_too_big(ctr, raw_cap)) return;
+    const unsigned long long n = ctr->n_raw, base = (unsigned long long)blockIdx.x * kSortChunk;
+    if (base >= n) {   // empty chunk: all padding
+        for (unsigned i = threadIdx.x; i < kSortChunk; i += blockDim.x) chunks[base + i] = ~0ull;
+        return;
+    }
+    for (unsigned i = threadIdx.x; i < kSortChunk; i += blockDim.x) keys[i] = base + i < n ? raw[base + i] : ~0ull;
+    __syncthreads();
+    const unsigned t = threadIdx.x;
+    for (unsigned k = 2; k <= kSortChunk; k <<= 1)
+        for (unsigned j = k >> 1; j > 0; j >>= 1) {
+            unsigned i = 2 * t - (t & (j - 1)), l = i | j;
+            unsigned long long a = keys[i], b = keys[l];
+            if ((a > b) == ((i & k) == 0)) {
+                keys[i] = b;
+                keys[l] = a;
+            }
+            __syncthreads();
+        }
+    for (unsigned i = threadIdx.x; i < kSortChunk; i += blockDim.x) chunks[base + i] = keys[i];
+}
+
+__global__ void __launch_bounds__(256) k_sort_merge(const unsigned long long *__restrict__ chunks, const ScanCounters *ctr, unsigned long long raw_cap,
+                                                    unsigned long long *__restrict__ sorted) {
+    if (sort_too_big(ctr, raw_cap)) return;
     const unsigned long long n = ctr->n_raw;
-    if (ctr->cand_overflow || ctr->raw_overflow || n > (unsigned long long)kSmallSort || n > raw_cap) {
+    const unsigned n_chunks = (unsigned)((n + kSortChunk - 1) / kSortChunk);
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_chunks * kSortChunk) return;
+    const unsigned c = i / kSortChunk;
+    const unsigned long long key = chunks[i];
+    unsigned rank = i % kSortChunk;
+    for (unsigned o = 0; o < n_chunks; o++) {
+        if (o == c) continue;
+        // elements of chunk o that sort before this key: strictly smaller, plus equal ones if o < c (stable)
+        const unsigned long long *q = chunks + (size_t)o * kSortChunk;
+        unsigned lo = 0, hi = kSortChunk;
+        while (lo < hi) {
+            unsigned mid = (lo + hi) >> 1;
+            unsigned long long v = q[mid];
+            if (v < key || (v == key && o < c)) lo = mid + 1; else hi = mid;
+        }
+        rank += lo;
+    }
+    sorted[rank] = key;
+}
+
+__global__ void __launch_bounds__(1024) k_sort_unique(const unsigned long long *__restrict__ sorted, const ScanCounters *ctr, unsigned long long raw_cap,
+                                                      unsigned long long *__restrict__ uniq, unsigned long long *n_unique, unsigned int *big_flag) {
+    if (sort_too_big(ctr, raw_cap)) {
         if (threadIdx.x == 0) {
             *n_unique = 0;
             *big_flag = 1;
         }
         return;
     }
-    unsigned m = 1024;
-    while (m < n) m <<= 1;
-    for (unsigned i = threadIdx.x; i < m; i += blockDim.x) keys[i] = i < n ? raw[i] : ~0ull;
-    __syncthreads();
-    for (unsigned k = 2; k <= m; k <<= 1)
-        for (unsigned j = k >> 1; j > 0; j >>= 1) {
-            for (unsigned t = threadIdx.x; t < m / 2; t += blockDim.x) {
-                unsigned i = 2 * t - (t & (j - 1));   // index with bit j clear
-                unsigned l = i | j;
-                unsigned long long a = keys[i], b = keys[l];
-                bool up = (i & k) == 0;
-                if ((a > b) == up) {
-                    keys[i] = b;
-                    keys[l] = a;
-                }
-            }
-            __syncthreads();
-        }
-    // unique: each thread owns m/1024 consecutive keys
-    const unsigned per = m / 1024, i0 = threadIdx.x * per;
-    unsigned cnt = 0;
-    for (unsigned i = i0; i < i0 + per; i++) cnt += (keys[i] != ~0ull) && (i == 0 || keys[i] != keys[i - 1]);
+    const unsigned n = (unsigned)ctr->n_raw;
+    constexpr unsigned per = kSmallSort / 1024;
+    // thread t owns keys t, t+1024, ... (coalesced); ranks need a scan per "row": do 16 block scans
     __shared__ unsigned long long tot;
-    unsigned long long at = block_exclusive_scan(cnt, &tot);
-    for (unsigned i = i0; i < i0 + per; i++)
-        if ((keys[i] != ~0ull) && (i == 0 || keys[i] != keys[i - 1])) uniq[at++] = keys[i];
+    unsigned long long base = 0;
+    for (unsigned r = 0; r < per; r++) {
+        unsigned i = r * 1024 + threadIdx.x;
+        if (r * 1024 >= n) break;   // uniform
+        bool keep = i < n && sorted[i] != ~0ull && (i == 0 || sorted[i] != sorted[i - 1]);
+        unsigned long long at = block_exclusive_scan(keep ? 1ull : 0ull, &tot);
+        if (keep) uniq[base + at] = sorted[i];
+        base += tot;
+        __syncthreads();
+    }
     if (threadIdx.x == 0) {
-        *n_unique = tot;
+        *n_unique = base;
         *big_flag = 0;
     }
 }
@@ -851,18 +1021,19 @@ __global__ void __launch_bounds__(256) k_line_starts(const uint8_t *__restrict__
 }
 
 template <int BITS>
-cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, uint32_t *tile_nl, unsigned long long *cand,
+cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, const uint4 *bitmap2, uint32_t bits2,
+                             uint32_t *tile_nl, unsigned long long *cand,
                              unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
-    size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
+    size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(1u << bits2) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
     cudaError_t e;
     if (fold) {
         e = cudaFuncSetAttribute(k_scan<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr);
     } else {
         e = cudaFuncSetAttribute(k_scan<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr);
     }
     return cudaGetLastError();
 }
@@ -882,14 +1053,15 @@ cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const D
         k_scan_nl_only<<<num_sms, kScanThreads, 0, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, tile_nl);
         return cudaGetLastError();
     }
-    const uint4 *bitmap = reinterpret_cast<const uint4 *>(fv.bitmap);
+    const uint4 *bitmap = reinterpret_cast<const uint4 *>(fv.bitmap), *bitmap2 = reinterpret_cast<const uint4 *>(fv.bitmap2);
+    const uint32_t bits2 = fv.log2_bits2;
     switch (fv.log2_bits) {
-        case 15: return launch_scan_bits<15>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 16: return launch_scan_bits<16>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 17: return launch_scan_bits<17>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 18: return launch_scan_bits<18>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 19: return launch_scan_bits<19>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 20: return launch_scan_bits<20>(fv.fold != 0, text, n_tiles, bitmap, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 15: return launch_scan_bits<15>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 16: return launch_scan_bits<16>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 17: return launch_scan_bits<17>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 18: return launch_scan_bits<18>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 19: return launch_scan_bits<19>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 20: return launch_scan_bits<20>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
         default: return cudaErrorInvalidValue;
     }
 }
@@ -911,9 +1083,11 @@ cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_pref
 }
 
 cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, const unsigned long long *cand,
-                           unsigned long long cand_cap, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+                           unsigned long long cand_cap, unsigned long long *tasks, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr,
+                           int num_sms, cudaStream_t s) {
     if (lib.fv.log2_bits == 0) return cudaSuccess;
-    k_confirm<<<num_sms * 4, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, lib.fv, pt, cand, cand_cap, raw, raw_cap, ctr);
+    k_confirm<<<num_sms * 8, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
+    k_verify<<<num_sms * 16, kVerifyWarps * 32, 0, s>>>(text, lib.blob, lib.h, pt, tasks, raw_cap, raw, raw_cap, ctr);
     return cudaGetLastError();
 }
 
@@ -978,12 +1152,12 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     return cudaGetLastError();
 }
 
-cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *uniq,
-                              unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s) {
-    size_t smem = (size_t)kSmallSort * 8;
-    cudaError_t e = cudaFuncSetAttribute(k_sort_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    k_sort_small<<<1, 1024, smem, s>>>(raw, ctr, raw_cap, uniq, n_unique, big_flag);
+cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
+                              unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s) {
+    unsigned long long *chunks = scratch, *sorted = scratch + kSmallSort;
+    k_sort_chunks<<<kSortChunks, kSortChunk / 2, 0, s>>>(raw, ctr, raw_cap, chunks);
+    k_sort_merge<<<kSmallSort / 256, 256, 0, s>>>(chunks, ctr, raw_cap, sorted);
+    k_sort_unique<<<1, 1024, 0, s>>>(sorted, ctr, raw_cap, uniq, n_unique, big_flag);
     return cudaGetLastError();
 }
 

@@ -26,10 +26,10 @@ constexpr int kMaxCtxLines = 1000;      // lines_before / lines_after / proximit
 // The gram filter in use on one device: device pointers into the blob as compiled, or into a
 // separately uploaded rebuild (profile-guided re-selection, pm_runtime.cu).
 struct FilterView {
-    const uint32_t *bitmap = nullptr, *gkeys = nullptr, *gfirst = nullptr, *gcount = nullptr;
+    const uint32_t *bitmap = nullptr, *bitmap2 = nullptr, *gkeys = nullptr, *gfirst = nullptr, *gcount = nullptr;
     const Probe *probes = nullptr;
     const uint8_t *litpool = nullptr;
-    uint32_t log2_bits = 0, log2_cap = 0, fold = 0, n_grams = 0;
+    uint32_t log2_bits = 0, log2_bits2 = 0, log2_cap = 0, fold = 0, n_grams = 0;
 };
 
 struct DeviceLibrary {
@@ -77,8 +77,10 @@ cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const D
 cudaError_t launch_prefix(const uint32_t *tile_nl, unsigned long long *tile_prefix, unsigned long long n_tiles,
                           unsigned long long *scratch, cudaStream_t s);
 cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_prefix, PodDev *pods, int n_pods, cudaStream_t s);
+// Two launches: k_confirm (candidate -> exact gram -> literal -> verify task) and k_verify (task ->
+// line -> verify DFA -> raw event).  `tasks` holds raw_cap u64.
 cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt,
-                           const unsigned long long *cand, unsigned long long cand_cap, unsigned long long *raw,
+                           const unsigned long long *cand, unsigned long long cand_cap, unsigned long long *tasks, unsigned long long *raw,
                            unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
 cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group,
                             unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
@@ -110,11 +112,12 @@ size_t resolve_aux_bytes();
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
                            const unsigned long long *uniq, const unsigned long long *n_events_dev, unsigned long long ev_cap, EventOut out,
                            const ResolveScratch &rs, int num_sms, cudaStream_t s);
-// Ordering + de-duplication in one CTA for ctr->n_raw <= kSmallSort (otherwise *big_flag = 1 and
+// Ordering + de-duplication without host involvement for ctr->n_raw <= kSmallSort (otherwise *big_flag = 1 and
 // the caller falls back to launch_sort_unique once it knows the count).
 constexpr int kSmallSort = 16384;
-cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *uniq,
-                              unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s);
+// Three launches; `scratch` holds 2 * kSmallSort u64.
+cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
+                              unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s);
 // Gram profile: counts, for every aligned word of text[0, sample_bytes), the occurrences of the
 // keys of an open-addressing table (keys: 2^log2_cap u32, kGramEmpty = free; counts zeroed by the
 // caller).  Used once per library to learn which literal grams are frequent in the real logs.

@@ -181,13 +181,17 @@ void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mo
         while (out.log2_bits < 20 && (1ull << out.log2_bits) < 512ull * out.n_grams) out.log2_bits++;
         while ((1u << out.log2_cap) < 2 * out.n_grams) out.log2_cap++;
     }
+    out.log2_bits2 = out.log2_bits ? std::min<uint32_t>(out.log2_bits, 18) : 0;
     out.bitmap.assign(out.log2_bits ? (1u << out.log2_bits) / 32 : 4, 0);
+    out.bitmap2.assign(out.log2_bits2 ? (1u << out.log2_bits2) / 32 : 4, 0);
     out.gkeys.assign(1u << out.log2_cap, kGramEmpty);
     out.gfirst.assign(1u << out.log2_cap, 0);
     out.gcount.assign(1u << out.log2_cap, 0);
     for (auto &kv : by_gram) {
         uint32_t bit = gram_filter_bit(kv.first, out.log2_bits);
         out.bitmap[bit >> 5] |= 1u << (bit & 31);
+        uint32_t bit2 = gram_filter_bit2(kv.first, out.log2_bits2);
+        out.bitmap2[bit2 >> 5] |= 1u << (bit2 & 31);
         uint32_t slot = gram_table_slot(kv.first, out.log2_cap);
         while (out.gkeys[slot] != kGramEmpty) slot = (slot + 1) & ((1u << out.log2_cap) - 1);
         out.gkeys[slot] = kv.first;
@@ -430,6 +434,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         h.n_secondaries = (uint32_t)sdesc.size();
         h.stack_unit = stack_unit;
         h.filter_log2_bits = log2_bits;
+        h.filter_log2_bits2 = fb.log2_bits2;
         h.filter_fold = fold;
         h.gram_log2_cap = log2_cap;
         h.n_grams = n_grams;
@@ -445,6 +450,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
             return at;
         };
         h.off_bitmap = place(bitmap.data(), bitmap.size() * 4);
+        h.off_bitmap2 = place(fb.bitmap2.data(), fb.bitmap2.size() * 4);
         h.off_gram_keys = place(gkeys.data(), gkeys.size() * 4);
         h.off_gram_first = place(gfirst.data(), gfirst.size() * 4);
         h.off_gram_count = place(gcount.data(), gcount.size() * 4);

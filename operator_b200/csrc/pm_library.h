@@ -25,9 +25,9 @@ struct PatternInfo {
 // the required literals of the tier-1 patterns.  Separate from the rest of the blob because the
 // runtime rebuilds it when it has measured which grams are frequent in the actual logs.
 struct FilterBuild {
-    uint32_t log2_bits = 0, log2_cap = 4, n_grams = 0, n_probes = 0;
+    uint32_t log2_bits = 0, log2_bits2 = 0, log2_cap = 4, n_grams = 0, n_probes = 0;
     bool fold = false;
-    std::vector<uint32_t> bitmap, gkeys, gfirst, gcount;
+    std::vector<uint32_t> bitmap, bitmap2, gkeys, gfirst, gcount;
     std::vector<Probe> probes;
     std::vector<uint8_t> litpool;
 };

@@ -168,6 +168,7 @@ struct DevWork {
     uint64_t cand_cap = 0, raw_cap = 0;
     Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, ev_soa, lines_tmp;
     Buf rs_items, rs_results, rs_long, rs_aux, rs_ctr, h_rs_ctr;   // resolve-stage scratch
+    Buf tasks, sort_scratch;
     uint64_t item_cap = 0, long_cap = 0, ev_cap = 0;
     int any_trailing_cr = 0;
     PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
@@ -224,7 +225,7 @@ void release_work(pm_batch *b) {
         Device *d = b->ctx->devs[w.slot];
         cudaSetDevice(d->id);
         if (w.stream) cudaStreamSynchronize(w.stream);
-        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.rs_ctr})
+        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.rs_ctr, &w.tasks, &w.sort_scratch})
             put(d->pool, *x);
         for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa, &w.h_rs_ctr}) put(b->ctx->pinned, *x);
         for (auto &ev : w.e)
@@ -419,10 +420,11 @@ int maybe_adapt(pm_library *l, DevWork &w) {
     build_filter(l->lib.literals, fold ? 1 : 0, &cost, fb);
     // ---- 3. upload the rebuilt sections and switch the view
     auto a16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
-    size_t o_bm = 0, o_k = a16(o_bm + fb.bitmap.size() * 4), o_f = a16(o_k + fb.gkeys.size() * 4), o_c = a16(o_f + fb.gfirst.size() * 4);
+    size_t o_bm = 0, o_b2 = a16(o_bm + fb.bitmap.size() * 4), o_k = a16(o_b2 + fb.bitmap2.size() * 4), o_f = a16(o_k + fb.gkeys.size() * 4), o_c = a16(o_f + fb.gfirst.size() * 4);
     size_t o_p = a16(o_c + fb.gcount.size() * 4), o_l = a16(o_p + fb.probes.size() * sizeof(Probe)), total = a16(o_l + fb.litpool.size()) + 16;
     std::vector<uint8_t> host(total, 0);
     memcpy(host.data() + o_bm, fb.bitmap.data(), fb.bitmap.size() * 4);
+    memcpy(host.data() + o_b2, fb.bitmap2.data(), fb.bitmap2.size() * 4);
     memcpy(host.data() + o_k, fb.gkeys.data(), fb.gkeys.size() * 4);
     memcpy(host.data() + o_f, fb.gfirst.data(), fb.gfirst.size() * 4);
     memcpy(host.data() + o_c, fb.gcount.data(), fb.gcount.size() * 4);
@@ -436,6 +438,8 @@ int maybe_adapt(pm_library *l, DevWork &w) {
     const uint8_t *db = reinterpret_cast<const uint8_t *>(dev);
     FilterView &fv = dl.fv;
     fv.bitmap = reinterpret_cast<const uint32_t *>(db + o_bm);
+    fv.bitmap2 = reinterpret_cast<const uint32_t *>(db + o_b2);
+    fv.log2_bits2 = fb.log2_bits2;
     fv.gkeys = reinterpret_cast<const uint32_t *>(db + o_k);
     fv.gfirst = reinterpret_cast<const uint32_t *>(db + o_f);
     fv.gcount = reinterpret_cast<const uint32_t *>(db + o_c);
@@ -519,18 +523,21 @@ int scan_async(pm_batch *b) {
         CU(cudaEventRecord(w.e[3], w.stream));
         CU(launch_prefix(w.tile_nl.as<uint32_t>(), w.tile_prefix.as<unsigned long long>(), w.n_tiles, w.scratch.as<unsigned long long>(), w.stream));
         CU(launch_pods(w.text.as<uint8_t>(), w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), np, w.stream));
-        CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.raw.as<unsigned long long>(),
-                          w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
-        w.launches += 1 + 3 + (np ? 1 : 0) + (dl.fv.log2_bits ? 1 : 0);
+        if ((rc = get(d->pool, w.raw_cap * 8, w.tasks))) return rc;
+        if ((rc = get(d->pool, 2 * (size_t)kSmallSort * 8, w.sort_scratch))) return rc;
+        CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.tasks.as<unsigned long long>(),
+                          w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
+        w.launches += 1 + 3 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
             CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, w.table(), (int)g, w.raw.as<unsigned long long>(), w.raw_cap,
                                w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
             w.launches++;
         }
-        CU(launch_sort_small(w.raw.as<unsigned long long>(), w.ctr.as<ScanCounters>(), w.raw_cap, w.uniq.as<unsigned long long>(),
+        CU(launch_sort_small(w.raw.as<unsigned long long>(), w.ctr.as<ScanCounters>(), w.raw_cap, w.sort_scratch.as<unsigned long long>(),
+                             w.uniq.as<unsigned long long>(),
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
                              reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream));
-        w.launches++;
+        w.launches += 3;
         CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream));
         CU(cudaEventRecord(w.e[4], w.stream));
         CU(cudaEventRecord(w.e[5], w.stream));
@@ -821,6 +828,8 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
             FilterView &fv = l->dev[d].fv;
             const uint8_t *db = l->dev[d].blob;
             fv.bitmap = reinterpret_cast<const uint32_t *>(db + bh.off_bitmap);
+            fv.bitmap2 = reinterpret_cast<const uint32_t *>(db + bh.off_bitmap2);
+            fv.log2_bits2 = bh.filter_log2_bits2;
             fv.gkeys = reinterpret_cast<const uint32_t *>(db + bh.off_gram_keys);
             fv.gfirst = reinterpret_cast<const uint32_t *>(db + bh.off_gram_first);
             fv.gcount = reinterpret_cast<const uint32_t *>(db + bh.off_gram_count);

@@ -113,6 +113,9 @@ int pmt_filter_triggers(pmt_lib *l, int p, const uint8_t *text, size_t n, int ph
         if (h->filter_fold) g |= 0x20202020u;
         uint32_t bit = gram_filter_bit(g, h->filter_log2_bits);
         if (!((bitmap[bit >> 5] >> (bit & 31)) & 1)) continue;
+        const uint32_t *bitmap2 = (const uint32_t *)(b + h->off_bitmap2);
+        uint32_t bit2 = gram_filter_bit2(g, h->filter_log2_bits2);
+        if (!((bitmap2[bit2 >> 5] >> (bit2 & 31)) & 1)) continue;
         uint32_t mask = (1u << h->gram_log2_cap) - 1, slot = gram_table_slot(g, h->gram_log2_cap);
         while (gk[slot] != kGramEmpty && gk[slot] != g) slot = (slot + 1) & mask;
         if (gk[slot] != g) continue;
