@@ -675,7 +675,7 @@ __global__ void __launch_bounds__(1024) k_sort_unique(const unsigned long long *
 //   k_check      thread per item (short lines); k_check_long: warp per item with a speculative
 //                chunked walk (every lane guesses its entry state, guesses are validated in order)
 //   k_finalize   thread per event: STACK run length, nearest secondary hit, fp64 score
-constexpr int kPlanWarps = 2;
+constexpr int kPlanWarps = 4;
 constexpr int kCtxSlots = kMaxCtxLines + 2;
 constexpr uint32_t kItemInvalid = 0xFFFFFFFFu;
 constexpr uint32_t kLongLine = 512;      // lines above this are walked by a whole warp
@@ -692,30 +692,37 @@ struct EvAux {
 };
 
 // Collects positions of the next `need` '\n' bytes at positions >= from into out[0..need).
+// Four 512-byte steps are loaded per round trip (the text around a hit is cold in L2/DRAM).
 __device__ void warp_collect_forward(const uint8_t *text, unsigned long long from, int need, unsigned long long *out) {
     const int lane = threadIdx.x & 31;
     unsigned long long a0 = from & ~15ull;
     int got = 0;
     while (got < need) {
-        unsigned long long a = a0 + (unsigned long long)lane * 16;
-        uint4 v = *reinterpret_cast<const uint4 *>(text + a);
-        uint32_t m = newline_mask16(v);
-        if (a < from) m &= (from - a >= 16) ? 0u : ~((1u << (from - a)) - 1u);
-        int c = __popc(m);
-        int inc = c;
+        uint4 v[4];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            int y = __shfl_up_sync(FULL, inc, o);
-            if (lane >= o) inc += y;
+        for (int u = 0; u < 4; u++) v[u] = *reinterpret_cast<const uint4 *>(text + a0 + u * 512 + (unsigned long long)lane * 16);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (got >= need) break;
+            unsigned long long a = a0 + u * 512 + (unsigned long long)lane * 16;
+            uint32_t m = newline_mask16(v[u]);
+            if (a < from) m &= (from - a >= 16) ? 0u : ~((1u << (from - a)) - 1u);
+            int c = __popc(m);
+            int inc = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(FULL, inc, o);
+                if (lane >= o) inc += y;
+            }
+            int rank = got + inc - c;
+            while (m && rank < need) {
+                int bpos = __ffs(m) - 1;
+                m &= m - 1;
+                out[rank++] = a + bpos;
+            }
+            got += __shfl_sync(FULL, inc, 31);
         }
-        int rank = got + inc - c;
-        while (m && rank < need) {
-            int bpos = __ffs(m) - 1;
-            m &= m - 1;
-            out[rank++] = a + bpos;
-        }
-        got += __shfl_sync(FULL, inc, 31);
-        a0 += 512;
+        a0 += 2048;
     }
     __syncwarp();
 }
@@ -759,11 +766,11 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
                                                           const unsigned long long *__restrict__ uniq, const unsigned long long *n_events_ptr,
                                                           unsigned long long ev_cap, EventOut out,
                                                           Item *__restrict__ items, unsigned long long item_cap, uint32_t *__restrict__ long_list,
-                                                          unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr) {
-    __shared__ unsigned long long fwd_s[kPlanWarps][kCtxSlots];   // fwd[i]: '\n' that ends line L+i
-    __shared__ unsigned long long bwd_s[kPlanWarps][kCtxSlots];   // bwd[i]: '\n' that precedes line L-i
+                                                          unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr, int slots) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned long long *fwd = fwd_s[warp], *bwd = bwd_s[warp];
+    unsigned long long *fwd = reinterpret_cast<unsigned long long *>(smem_raw) + (size_t)warp * 2 * slots;   // fwd[i]: '\n' that ends line L+i
+    unsigned long long *bwd = fwd + slots;                                                                   // bwd[i]: '\n' that precedes line L-i
     const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
     const PodDev *pods = pt.pods;
@@ -1142,8 +1149,14 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     unsigned blocks = (unsigned)((ev_cap + kPlanWarps - 1) / kPlanWarps);
     if (blocks > (unsigned)num_sms * 16u) blocks = (unsigned)num_sms * 16u;
     Item *items = reinterpret_cast<Item *>(rs.items);
-    k_plan<<<blocks, kPlanWarps * 32, 0, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events_dev, ev_cap, out, items, rs.item_cap, rs.long_list,
-                                              rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr);
+    int slots = lib.ctx_slots > 0 ? lib.ctx_slots : kCtxSlots;
+    size_t plan_smem = (size_t)kPlanWarps * 2 * slots * 8;
+    if (plan_smem > 48 * 1024) {
+        e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem);
+        if (e != cudaSuccess) return e;
+    }
+    k_plan<<<blocks, kPlanWarps * 32, plan_smem, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events_dev, ev_cap, out, items, rs.item_cap,
+                                                      rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots);
     k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
     k_check_long<<<num_sms * 8, 128, 0, s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
     unsigned fb = (unsigned)((ev_cap + 127) / 128);

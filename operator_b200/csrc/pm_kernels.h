@@ -35,6 +35,7 @@ struct FilterView {
 struct DeviceLibrary {
     const uint8_t *blob = nullptr;      // device copy of the compiled blob
     FilterView fv;
+    int ctx_slots = 0;                  // newline slots k_plan needs per direction (largest window of the library + 2)
     BlobHeader h;                       // host copy of the blob header
 };
 

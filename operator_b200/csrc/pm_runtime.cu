@@ -839,6 +839,18 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
             fv.log2_cap = bh.gram_log2_cap;
             fv.fold = bh.filter_fold;
             fv.n_grams = bh.n_grams;
+            {   // largest context / proximity window of the library -> shared-memory slots of k_plan
+                const uint8_t *hb = l->lib.blob.data();
+                const PatternDesc *pdv = reinterpret_cast<const PatternDesc *>(hb + bh.off_patterns);
+                const SecDesc *sdv = reinterpret_cast<const SecDesc *>(hb + bh.off_secondaries);
+                int need = 1;
+                for (uint32_t i = 0; i < bh.n_patterns; i++) {
+                    need = std::max(need, std::max(pdv[i].lines_before, pdv[i].lines_after));
+                    if (pdv[i].include_stack) need = std::max(need, kStackMax);
+                }
+                for (uint32_t i = 0; i < bh.n_secondaries; i++) need = std::max(need, sdv[i].window);
+                l->dev[d].ctx_slots = need + 2;
+            }
         }
     }
     pm_library *old;
