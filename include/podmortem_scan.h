@@ -141,6 +141,30 @@ int pm_batch_rescan(pm_batch *, pm_result_view *out);
  * (host memory, capacity `cap` entries); returns the number of lines or a negative status. */
 int64_t pm_batch_line_index(pm_batch *, int pod, int64_t *out, int64_t cap);
 
+/* ---- line table without allocation ------------------------------------------------------ */
+/* No counterpart in the reference: this entry point exists for callers of THIS library that are
+ * given device buffers but may not create any themselves -- a plugin inside a host process that
+ * hands out all GPU memory from its own pool, a latency-critical path that cannot afford
+ * cudaMalloc's device-wide synchronisation, a job whose memory budget was fixed at start-up.
+ * All other entry points draw working memory from the context's pool, which grows with
+ * cudaMalloc; this one calls no allocator at all.  Its scratch is a fixed array inside the
+ * loaded module (about 257 KiB on every GPU that loads the library, held until exit), hence:
+ *   - n_bytes may not exceed PM_NOALLOC_MAX_BYTES; larger inputs are refused with PM_E_INVALID
+ *     (message via pm_noalloc_last_error) and nothing is launched;
+ *   - all calls on one GPU share that array: two calls whose kernels can overlap on the device
+ *     (different streams, different host threads) race on it and corrupt each other's result.
+ *     Serialise them: same stream, or an event between them;
+ *   - the first call on each GPU looks up the array's device address (with that GPU current);
+ *     make that first call outside any stream capture.
+ * d_text, d_line_start and d_n_lines are DEVICE pointers supplied by the caller; the current
+ * device must be the one they live on.  d_line_start[i] receives the byte offset of line i for
+ * i < min(*d_n_lines, cap), with the line model of SPEC.md section 2 (the same table
+ * pm_batch_line_index returns); *d_n_lines receives the line count.  The work is enqueued on
+ * `stream` (a cudaStream_t, NULL = default stream); results are valid once it has run. */
+#define PM_NOALLOC_MAX_BYTES (64ull << 20)
+int pm_line_index_noalloc(const uint8_t *d_text, uint64_t n_bytes, int64_t *d_line_start, uint64_t cap, uint64_t *d_n_lines, void *stream);
+const char *pm_noalloc_last_error(void);
+
 /* ---- the /parse contract as one call (a3, a4, a14) -------------------------------------- */
 /* request_json: the PodFailureData body the operator posts (PodFailureWatcher.java:334;
  * fields used: "logs", and pod.metadata.name/namespace for the echo).  On success *response is

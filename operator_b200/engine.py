@@ -68,7 +68,8 @@ _dll = None
 ABI_SYMBOLS = ["pm_abi_version", "pm_init", "pm_init_devices", "pm_shutdown", "pm_last_error", "pm_device_count", "pm_library_compile",
                "pm_library_publish", "pm_library_free", "pm_library_pattern_count", "pm_library_pattern_meta_json",
                "pm_host_alloc", "pm_host_free", "pm_batch_begin", "pm_batch_add_pod", "pm_batch_submit", "pm_batch_wait",
-               "pm_batch_release", "pm_batch_stage", "pm_batch_rescan", "pm_batch_line_index", "pm_parse"]
+               "pm_batch_release", "pm_batch_stage", "pm_batch_rescan", "pm_batch_line_index", "pm_parse",
+               "pm_line_index_noalloc", "pm_noalloc_last_error"]
 
 
 def load_library() -> ctypes.CDLL:
@@ -110,6 +111,8 @@ def load_library() -> ctypes.CDLL:
     d.pm_batch_line_index.argtypes = [vp, ctypes.c_int, _P(ctypes.c_int64), ctypes.c_int64]
     d.pm_batch_line_index.restype = ctypes.c_int64
     d.pm_parse.argtypes = [vp, ctypes.c_char_p, sz, _P(ctypes.c_char_p), _P(sz)]
+    d.pm_line_index_noalloc.argtypes = [vp, ctypes.c_uint64, vp, ctypes.c_uint64, vp, vp]
+    d.pm_noalloc_last_error.restype = ctypes.c_char_p
     _dll = d
     return d
 
