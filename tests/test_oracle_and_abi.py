@@ -174,7 +174,10 @@ print("rank", rank, "ok", mine)
 def test_sharding_and_reductions_under_gloo(tmp_path):
     script = tmp_path / "worker.py"
     script.write_text(_WORKER % ROOT)
-    port = 29500 + os.getpid() % 2000
+    import socket
+    with socket.socket() as sk:          # a port that is free right now
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", str(port), str(script)], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
