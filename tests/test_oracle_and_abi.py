@@ -167,7 +167,7 @@ slow = dist.max_over_ranks(1.0 + rank)
 assert total == sum(sizes), total
 assert slow == float(world), slow
 assert sorted(i for s in shards for i in s) == list(range(len(sizes)))
-os.write(1, ("rank %d ok %d\n" % (rank, mine)).encode())   # one syscall: the two ranks share the pipe
+os.write(1, ("rank " + str(rank) + " ok " + str(mine) + "\n").encode())   # one syscall: the two ranks share the pipe
 """
 
 
