@@ -24,7 +24,7 @@
 namespace pm {
 
 constexpr uint32_t kBlobMagic = 0x424C4D50u;   // "PMLB"
-constexpr uint32_t kBlobVersion = 5;
+constexpr uint32_t kBlobVersion = 6;
 constexpr int kGramLen = 4;        // bytes per gram = one aligned 32-bit text word
 constexpr int kMinLiteral = 7;     // any 7-byte window covers one aligned 4-byte word
 constexpr uint32_t kGramEmpty = 0xFFFFFFFFu;   // 0xFF never occurs in valid UTF-8
@@ -75,11 +75,17 @@ struct SecDesc {
     uint32_t unit;
 };
 
+// Combined scan DFA of one group, in the form k_dfa_scan walks: END-OF-LINE is folded into the
+// '\n' byte (its targets are "terminal twins" whose rows equal the start-of-line row, so the
+// kernel needs no newline branch), entries are premultiplied by the row stride.
+//   wide:       256 columns, index = state*256 + byte                (one lookup per byte)
+//   compressed: stride columns, index = state*stride + classmap[byte]
 struct GroupDesc {
     uint32_t table_off;      // u16 elements from off_tables
     uint32_t classmap_off;
     uint32_t accept_off;     // u32 elements from off_group_accept: (nstates-first_accept+1) starts, then lists
-    uint16_t nstates, stride, first_accept, pad;
+    uint16_t nstates, stride, first_accept, mid_state;
+    uint32_t wide, pad;
 };
 
 constexpr uint32_t kFilterMult0 = 0x9E3779B1u;   // default multiplier; the runtime may reseed (pm_runtime.cu)

@@ -512,49 +512,218 @@ __global__ void __launch_bounds__(256) k_gram_profile(const uint4 *__restrict__ 
 }
 
 // ------------------------------------------------------------------------------------ k_dfa_scan
-// Combined search DFA of the patterns that have no 7-byte literal.  Transition table and class
-// map live in shared memory; every thread owns the lines that START inside its chunk and keeps
-// walking past the chunk end until that last line is finished (overlapping chunks), so no
-// state crosses threads.  Correctness first: text is read through L1 here; the filter path
-// above is the one built for bandwidth.
-constexpr int kDfaThreads = 256, kDfaChunk = 256;
+// Combined search DFA of the patterns that have no 7-byte literal (the kernel north_star
+// sketches: multi-pattern DFA, transition table in shared memory, overlapping chunks).
+//
+//  * One persistent CTA per SM owns a contiguous range of 64 KiB tiles and streams them through
+//    a double buffer with cp.async (16-byte pieces, 128-byte rows XOR-swizzled so that the 32
+//    lanes of a warp, each walking its own 128-byte row, read conflict-free 128-bit pieces).
+//  * The table has END-OF-LINE folded into the '\n' byte (pm_library.cc, build_scan_table), so
+//    the walk has no newline branch and a thread's chunk may start anywhere in a line.
+//  * A thread does not know the DFA state at the start of its chunk.  It guesses: mid-line idle
+//    state, warmed up over the 32 bytes in front of the chunk (the overlap).  After the walk the
+//    guesses are validated against the true exit state of the previous chunk, in order; a wrong
+//    guess re-walks that one chunk.  Exact, and on log text the guesses are almost always right.
+//  * The hot walk only tracks "was any accepting state seen".  Chunks where one was seen (rare)
+//    are walked once more from their validated entry state to emit (line_start, pattern) events.
+//  * CTA ranges are cut at line starts (a CTA finishes the line that crosses its upper bound), so
+//    the first chunk of a range starts in the exact start-of-line state.
+constexpr int kDfaThreads = 512, kDfaChunk = 128, kDfaTile = kDfaThreads * kDfaChunk, kDfaWarm = 32;
 
-__global__ void __launch_bounds__(kDfaThreads) k_dfa_scan(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h, PodTable pt, int group,
-                                                          unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;"); }
+
+// byte `off` of row `row` in a swizzled tile buffer
+__device__ __forceinline__ uint32_t dfa_tile_byte(const uint8_t *buf, int row, int off) {
+    return buf[row * kDfaChunk + ((((off >> 4) ^ (row & 7))) << 4) + (off & 15)];
+}
+
+struct DfaCtx {
+    const uint16_t *tab;      // shared memory, entries premultiplied by the row stride
+    const uint8_t *cmap;      // shared memory (compressed form only)
+    const uint8_t *text;      // global, for the rare look-ahead / look-behind
+    unsigned long long tile_start;
+    uint32_t first_accept_p;  // first accepting state, premultiplied
+    PodTable pt;
+};
+
+template <bool WIDE>
+__device__ __forceinline__ uint32_t dfa_next(const DfaCtx &c, uint32_t s, uint32_t b) {
+    return WIDE ? c.tab[s + b] : c.tab[s + c.cmap[b]];
+}
+
+// '\r' directly in front of a separator '\n' is not part of the line: feed END-OF-LINE ('\n') for it.
+__device__ __forceinline__ uint32_t dfa_cr_fix(const DfaCtx &c, uint32_t b, unsigned long long pos) {
+    if (b == '\r' && c.text[pos + 1] == '\n' && !(c.pt.any_trailing_cr && is_pod_raw_end(c.pt, pos + 1))) return '\n';
+    return b;
+}
+
+// Walks bytes [lo, hi) of the thread's row; returns the exit state, accumulates the largest state seen.
+template <bool WIDE>
+__device__ __forceinline__ uint32_t dfa_walk(const DfaCtx &c, const uint8_t *buf, int row, int lo, int hi, uint32_t s, uint32_t &smax) {
+    if (lo == 0 && hi == kDfaChunk) {
+#pragma unroll 2
+        for (int k = 0; k < 8; k++) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(buf + row * kDfaChunk + ((k ^ (row & 7)) << 4));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                uint32_t b = (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu;
+                if (b == '\r') b = dfa_cr_fix(c, b, c.tile_start + (unsigned long long)row * kDfaChunk + k * 16 + j);
+                s = dfa_next<WIDE>(c, s, b);
+                smax = max(smax, s);
+            }
+        }
+    } else {
+        for (int off = lo; off < hi; off++) {
+            uint32_t b = dfa_tile_byte(buf, row, off);
+            if (b == '\r') b = dfa_cr_fix(c, b, c.tile_start + (unsigned long long)row * kDfaChunk + off);
+            s = dfa_next<WIDE>(c, s, b);
+            smax = max(smax, s);
+        }
+    }
+    return s;
+}
+
+template <bool WIDE>
+__global__ void __launch_bounds__(kDfaThreads, 1) k_dfa_scan(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h,
+                                                             PodTable pt, int group, unsigned long long *__restrict__ raw, unsigned long long raw_cap,
+                                                             ScanCounters *ctr) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ uint16_t exit_s[kDfaThreads];
+    __shared__ unsigned long long own_s[2];
+    __shared__ uint32_t carry_s;
     const GroupDesc gd = reinterpret_cast<const GroupDesc *>(blob + h.off_groups)[group];
     const uint16_t *gtab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + gd.table_off;
-    const uint8_t *gcm = blob + h.off_classmaps + gd.classmap_off;
     const uint32_t *acc = reinterpret_cast<const uint32_t *>(blob + h.off_group_accept) + gd.accept_off;
-    uint8_t *cmap = smem_raw;
-    uint16_t *tab = reinterpret_cast<uint16_t *>(smem_raw + 256);
     const uint32_t n_entries = (uint32_t)gd.nstates * gd.stride;
-    for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) cmap[i] = gcm[i];
-    for (uint32_t i = threadIdx.x; i < n_entries; i += blockDim.x) tab[i] = gtab[i];
+    // shared memory: [tile buffer 0][tile buffer 1][table][class map]
+    uint8_t *bufs[2] = {smem_raw, smem_raw + kDfaTile};
+    uint16_t *tab = reinterpret_cast<uint16_t *>(smem_raw + 2 * kDfaTile);
+    uint8_t *cmap = reinterpret_cast<uint8_t *>(tab) + (((size_t)n_entries * 2 + 15) & ~(size_t)15);
+    const int tid = threadIdx.x;
+    for (uint32_t i = tid; i < (n_entries + 7) / 8; i += kDfaThreads)
+        reinterpret_cast<uint4 *>(tab)[i] = reinterpret_cast<const uint4 *>(gtab)[i];   // table start is 16-byte aligned in the blob
+    if (!WIDE && tid < 64) reinterpret_cast<uint32_t *>(cmap)[tid] = reinterpret_cast<const uint32_t *>(blob + h.off_classmaps + gd.classmap_off)[tid];
+
+    // ---- this CTA's range of tiles, cut at line starts
+    const unsigned long long n_tiles = (total + kDfaTile - 1) / kDfaTile;
+    const unsigned long long per = (n_tiles + gridDim.x - 1) / gridDim.x;
+    const unsigned long long seg_lo = min((unsigned long long)blockIdx.x * per * kDfaTile, total);
+    const unsigned long long seg_hi = min(((unsigned long long)blockIdx.x + 1) * per * kDfaTile, total);
+    if (tid < 2) {
+        // first line start at or after `x` (x = 0: the buffer starts with '\n' padding, position 0 is fine)
+        unsigned long long x = tid == 0 ? seg_lo : seg_hi, q = x;
+        if (x > 0 && x < total) {
+            q = x - 1;
+            while (q < total && text[q] != '\n') q++;
+            q = min(q + 1, total);
+        }
+        own_s[tid] = q;
+    }
+    if (tid == 0) carry_s = 0;
     __syncthreads();
-    const uint32_t stride = gd.stride, first_accept = gd.first_accept;
-    const unsigned long long n_chunks = (total - kHeaderBytes + kDfaChunk - 1) / kDfaChunk;
-    for (unsigned long long c = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; c < n_chunks; c += (unsigned long long)gridDim.x * blockDim.x) {
-        unsigned long long cb = kHeaderBytes + c * kDfaChunk, ce = cb + kDfaChunk;
-        if (ce > total) ce = total;
-        // first line start in [cb, ce): the byte after the first '\n' at position >= cb - 1
-        unsigned long long p = cb - 1;
-        while (p < ce && text[p] != '\n') p++;
-        p++;
-        while (p < ce) {   // p is a line start inside the chunk
-            unsigned long long ls = p;
-            uint32_t s = 0, last_emit = 0xFFFFFFFFu;
-            for (;;) {
-                uint8_t b = text[p];
-                // a line ends at '\n', or at the '\r' of a "\r\n" separator (SPEC.md section 2)
-                bool crlf = (b == '\r') && text[p + 1] == '\n' && !(pt.any_trailing_cr && is_pod_raw_end(pt, p + 1));
-                bool eol = (b == '\n') || crlf;
-                if (crlf) p++;
-                s = tab[s * stride + (eol ? stride - 1 : cmap[b])];
-                if (s >= first_accept && s != last_emit) {
+    const unsigned long long own_lo = own_s[0], own_hi = own_s[1];
+    if (own_lo >= own_hi) return;
+
+    DfaCtx c;
+    c.tab = tab;
+    c.cmap = cmap;
+    c.text = text;
+    c.pt = pt;
+    c.first_accept_p = (uint32_t)gd.first_accept * gd.stride;
+    const uint32_t mid_p = (uint32_t)gd.mid_state * gd.stride;
+
+    const unsigned long long t_first = own_lo / kDfaTile, t_last = (own_hi - 1) / kDfaTile;
+    auto issue = [&](unsigned long long t, uint8_t *buf) {   // 8 x 16-byte pieces per thread, coalesced, swizzled on the way in
+        const unsigned long long ts = t * kDfaTile;
+#pragma unroll
+        for (int i = 0; i < kDfaTile / 16 / kDfaThreads; i++) {
+            const int q = i * kDfaThreads + tid, r = q >> 3, j = q & 7;
+            const unsigned long long g = ts + (unsigned long long)q * 16;
+            if (g + 16 <= total) cp_async16(buf + r * kDfaChunk + ((j ^ (r & 7)) << 4), text + g);
+        }
+        cp_async_commit();
+    };
+    issue(t_first, bufs[0]);
+    for (unsigned long long t = t_first; t <= t_last; t++) {
+        uint8_t *buf = bufs[(t - t_first) & 1];
+        cp_async_wait_all();
+        __syncthreads();                                     // tile t landed; everyone is done with the other buffer
+        if (t < t_last) issue(t + 1, bufs[(t - t_first + 1) & 1]);
+        c.tile_start = t * kDfaTile;
+        // ---- phase A: speculative walk of this thread's chunk, clipped to the CTA's range
+        const unsigned long long cs = c.tile_start + (unsigned long long)tid * kDfaChunk;
+        const unsigned long long a = max(cs, own_lo), b = min(cs + kDfaChunk, own_hi);
+        const bool active = a < b;
+        const bool exact = active && a == own_lo;            // starts at a line start: state 0 is the truth
+        const int lo = active ? (int)(a - cs) : 0, hi = active ? (int)(b - cs) : 0;
+        uint32_t guess = 0, ex = 0, smax = 0;
+        if (active) {
+            if (!exact) {
+                uint32_t s = mid_p, dummy = 0;
+                if (lo > 0) {                                // clipped chunk that is not the range start cannot happen; keep it safe
+                    s = dfa_walk<WIDE>(c, buf, tid, max(0, lo - kDfaWarm), lo, s, dummy);
+                } else if (tid > 0) {
+                    s = dfa_walk<WIDE>(c, buf, tid - 1, kDfaChunk - kDfaWarm, kDfaChunk, s, dummy);
+                } else {                                     // row 0: the bytes in front of it are in the previous tile
+                    for (unsigned long long p = cs - kDfaWarm; p < cs; p++) {
+                        uint32_t bb = text[p];
+                        if (bb == '\r') bb = dfa_cr_fix(c, bb, p);
+                        s = dfa_next<WIDE>(c, s, bb);
+                    }
+                }
+                guess = s;
+            }
+            ex = dfa_walk<WIDE>(c, buf, tid, lo, hi, guess, smax);
+        }
+        // ---- phase B: validate the guesses in chunk order
+        const int t0 = (int)((max(c.tile_start, own_lo) - c.tile_start) / kDfaChunk);   // first active row
+        exit_s[tid] = (uint16_t)ex;
+        __syncthreads();
+        for (;;) {
+            bool wrong = false;
+            uint32_t truth = 0;
+            if (active && !exact) {
+                truth = tid == t0 ? carry_s : exit_s[tid - 1];
+                wrong = truth != guess;
+            }
+            if (!__syncthreads_or(wrong)) break;
+            if (wrong) {
+                guess = truth;
+                smax = 0;
+                ex = dfa_walk<WIDE>(c, buf, tid, lo, hi, guess, smax);
+                exit_s[tid] = (uint16_t)ex;
+            }
+            __syncthreads();
+        }
+        // last active row's exit state is the next tile's carry
+        const int t1 = (int)((min(c.tile_start + (unsigned long long)kDfaTile, own_hi) - 1 - c.tile_start) / kDfaChunk);
+        __syncthreads();
+        if (tid == t1) carry_s = ex;
+        // ---- phase C: emit (rare): walk again from the validated entry state
+        if (active && smax >= c.first_accept_p) {
+            uint32_t s = guess, last_emit = 0xFFFFFFFFu;
+            long long last_nl = -1;                          // position of the last '\n' before the current byte, if seen in this chunk
+            for (int off = lo; off < hi; off++) {
+                const unsigned long long pos = cs + off;
+                uint32_t bb = dfa_tile_byte(buf, tid, off);
+                if (bb == '\r') bb = dfa_cr_fix(c, bb, pos);
+                s = dfa_next<WIDE>(c, s, bb);
+                if (s >= c.first_accept_p && s != last_emit) {
                     last_emit = s;
-                    uint32_t a0 = acc[s - first_accept], a1 = acc[s - first_accept + 1];
-                    for (uint32_t k = a0; k < a1; k++) {
+                    unsigned long long ls;
+                    if (last_nl >= 0) {
+                        ls = (unsigned long long)last_nl + 1;
+                    } else {
+                        ls = pos;                            // line start lies before this chunk: look behind in the text
+                        while (text[ls - 1] != '\n') ls--;
+                    }
+                    const uint32_t sid = s / gd.stride - gd.first_accept;
+                    for (uint32_t k = acc[sid], ke = acc[sid + 1]; k < ke; k++) {
                         unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
                         if (at < raw_cap)
                             raw[at] = (ls << kPatternBits) | acc[k];
@@ -562,8 +731,11 @@ __global__ void __launch_bounds__(kDfaThreads) k_dfa_scan(const uint8_t *__restr
                             ctr->raw_overflow = 1;
                     }
                 }
-                p++;
-                if (eol) break;
+                if (bb == '\n') {
+                    last_nl = (long long)pos;
+                    if (text[pos] == '\r') last_nl = (long long)pos + 1;   // CRLF: the '\r' stood in for the separator
+                    last_emit = 0xFFFFFFFFu;
+                }
             }
         }
     }
@@ -1098,13 +1270,19 @@ cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, 
     return cudaGetLastError();
 }
 
-cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group, unsigned long long *raw,
-                            unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
-    // host copy of the group's size is not kept: budget the shared memory for the compiler's limit
-    size_t smem = 256 + 96 * 1024;
-    cudaError_t e = cudaFuncSetAttribute(k_dfa_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    k_dfa_scan<<<num_sms * 2, kDfaThreads, smem, s>>>(text, total_bytes, lib.blob, lib.h, pt, group, raw, raw_cap, ctr);
+cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group, bool wide,
+                            size_t table_bytes, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    size_t smem = 2 * (size_t)kDfaTile + ((table_bytes + 15) & ~(size_t)15) + 256;
+    cudaError_t e;
+    if (wide) {
+        e = cudaFuncSetAttribute(k_dfa_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k_dfa_scan<true><<<num_sms, kDfaThreads, smem, s>>>(text, total_bytes, lib.blob, lib.h, pt, group, raw, raw_cap, ctr);
+    } else {
+        e = cudaFuncSetAttribute(k_dfa_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k_dfa_scan<false><<<num_sms, kDfaThreads, smem, s>>>(text, total_bytes, lib.blob, lib.h, pt, group, raw, raw_cap, ctr);
+    }
     return cudaGetLastError();
 }
 

@@ -83,8 +83,9 @@ cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_pref
 cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt,
                            const unsigned long long *cand, unsigned long long cand_cap, unsigned long long *tasks, unsigned long long *raw,
                            unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
-cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group,
-                            unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
+// wide / table_bytes: from the group's descriptor (GroupDesc.wide, nstates * stride * 2).
+cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group, bool wide,
+                            size_t table_bytes, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
 // Sorts raw[0, n) and removes duplicates; *n_unique (device) receives the count.  temp/temp_bytes:
 // scratch from sort_temp_bytes(n).
 size_t sort_temp_bytes(unsigned long long n);

@@ -15,7 +15,7 @@ namespace {
 
 constexpr int kUnitMaxStates = 4096;       // verify DFA of one regex
 constexpr int kUnitNfaBudget = 20000;
-constexpr int kGroupTableBytes = 96 * 1024;   // combined DFA must fit shared memory next to the text tile
+constexpr int kGroupTableBytes = 64 * 1024;   // combined DFA table: shared memory next to two 64 KiB text tiles (k_dfa_scan)
 constexpr int kGroupMaxStates = 8192;
 constexpr int kGroupNfaBudget = 400000;
 
@@ -97,6 +97,7 @@ void compile_unit(const std::string &rx, int pattern, int secondary, const std::
 
 struct GroupBuild {
     Dfa dfa;
+    ScanTable scan;
     std::vector<int> patterns;
 };
 
@@ -109,7 +110,7 @@ void build_groups(const std::vector<int> &pats, const std::vector<NodePtr> &asts
     for (size_t u = 0; u < pats.size() && ok; u++) ok = nfa.add(*asts[pats[u]], (int)u, kGroupNfaBudget);
     GroupBuild g;
     if (ok) ok = build_search_dfa(nfa, /*early_accept=*/false, kGroupMaxStates, g.dfa);
-    if (ok) ok = (size_t)g.dfa.nstates * g.dfa.stride() * 2 <= (size_t)kGroupTableBytes;
+    if (ok) ok = build_scan_table(g.dfa, (size_t)kGroupTableBytes, g.scan);
     if (ok) {
         g.patterns = pats;
         out.push_back(std::move(g));
@@ -126,6 +127,67 @@ void build_groups(const std::vector<int> &pats, const std::vector<NodePtr> &asts
 size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
 }  // namespace
+
+bool build_scan_table(const Dfa &d, size_t max_bytes, ScanTable &out) {
+    out = ScanTable();
+    const int n = d.nstates, st = d.stride(), eolc = d.ncls;
+    // terminal twins: one per distinct END-OF-LINE target; their rows are the start-of-line row
+    std::map<int, int> twin;   // original EOL target -> index among twins
+    for (int s = 0; s < n; s++) twin.emplace((int)d.next[(size_t)s * st + eolc], 0);
+    int k = 0;
+    for (auto &kv : twin) kv.second = k++;
+    const int total = n + (int)twin.size();
+    auto accepting = [&](int s) { return s < n ? s >= d.first_accept : false; };
+    std::vector<int> twin_of(twin.size());
+    for (auto &kv : twin) twin_of[kv.second] = kv.first;
+    auto is_acc = [&](int s) { return s < n ? accepting(s) : accepting(twin_of[s - n]); };
+    // renumber: state 0 first, non-accepting, then accepting
+    std::vector<int> order, newid(total);
+    order.push_back(0);
+    for (int s = 1; s < total; s++)
+        if (!is_acc(s)) order.push_back(s);
+    out.first_accept = (int)order.size();
+    for (int s = 1; s < total; s++)
+        if (is_acc(s)) order.push_back(s);
+    for (int i = 0; i < total; i++) newid[order[i]] = i;
+    out.nstates = total;
+    if (total > 65535) return false;
+    // transition of (old numbering) state s on raw byte b
+    auto step = [&](int s, int b) -> int {
+        int row = s < n ? s : 0;   // twins behave like the start-of-line state
+        if (b == '\n') return n + twin[(int)d.next[(size_t)row * st + eolc]];
+        return (int)d.next[(size_t)row * st + d.classmap[b]];
+    };
+    out.wide = (size_t)total * 256 * 2 <= max_bytes && (size_t)total * 256 < 65536;
+    if (out.wide) {
+        out.stride = 256;
+        out.tab.resize((size_t)total * 256);
+        for (int i = 0; i < total; i++)
+            for (int b = 0; b < 256; b++) out.tab[(size_t)i * 256 + b] = (uint16_t)(newid[step(order[i], b)] * 256);
+    } else {
+        out.stride = d.ncls + 1;
+        if ((size_t)total * out.stride * 2 > max_bytes || (size_t)total * out.stride >= 65536) return false;
+        memcpy(out.cmap, d.classmap, 256);
+        out.cmap[(int)'\n'] = (uint8_t)eolc;
+        // representative byte per class
+        std::vector<int> repb(d.ncls, -1);
+        for (int b = 255; b >= 0; b--)
+            if (b != '\n') repb[d.classmap[b]] = b;
+        out.tab.assign((size_t)total * out.stride, 0);
+        for (int i = 0; i < total; i++) {
+            for (int c = 0; c < d.ncls; c++)
+                if (repb[c] >= 0) out.tab[(size_t)i * out.stride + c] = (uint16_t)(newid[step(order[i], repb[c])] * out.stride);
+            out.tab[(size_t)i * out.stride + eolc] = (uint16_t)(newid[step(order[i], '\n')] * out.stride);
+        }
+    }
+    out.mid_state = newid[step(0, 0x01)];
+    for (int i = out.first_accept; i < total; i++) {
+        int s = order[i];
+        int orig = s < n ? s : twin_of[s - n];
+        out.accept.push_back(d.accept[orig - d.first_accept]);
+    }
+    return true;
+}
 
 void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mode, const GramCostFn *cost, FilterBuild &out) {
     out = FilterBuild();
@@ -406,21 +468,27 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         for (auto &g : groups) {
             GroupDesc gd;
             memset(&gd, 0, sizeof gd);
-            put_dfa(g.dfa, gd.table_off, gd.classmap_off);
-            gd.nstates = (uint16_t)g.dfa.nstates;
-            gd.stride = (uint16_t)g.dfa.stride();
-            gd.first_accept = (uint16_t)g.dfa.first_accept;
+            gd.classmap_off = (uint32_t)classmaps.push_raw(g.scan.cmap, 256);
+            while (tables.bytes.size() % 16) tables.bytes.push_back(0);   // 16-byte aligned for bulk copies
+            gd.table_off = (uint32_t)(tables.bytes.size() / 2);
+            tables.push_raw(g.scan.tab.data(), g.scan.tab.size() * 2);
+            gd.nstates = (uint16_t)g.scan.nstates;
+            gd.stride = (uint16_t)g.scan.stride;
+            gd.first_accept = (uint16_t)g.scan.first_accept;
+            gd.mid_state = (uint16_t)g.scan.mid_state;
+            gd.wide = g.scan.wide;
             gd.accept_off = (uint32_t)(gaccept.bytes.size() / 4);
-            uint32_t na = (uint32_t)g.dfa.accept.size(), run = na + 1;
+            uint32_t na = (uint32_t)g.scan.accept.size(), run = na + 1;
             for (uint32_t a = 0; a < na; a++) {
                 gaccept.push(run);
-                run += (uint32_t)g.dfa.accept[a].size();
+                run += (uint32_t)g.scan.accept[a].size();
             }
             gaccept.push(run);
-            for (auto &lst : g.dfa.accept)
+            for (auto &lst : g.scan.accept)
                 for (int u : lst) gaccept.push((uint32_t)g.patterns[u]);
             groups_sec.push(gd);
             out.group_dfas.push_back(g.dfa);
+            out.group_scan.push_back(g.scan);
             out.group_patterns.push_back(g.patterns);
         }
 

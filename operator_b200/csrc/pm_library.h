@@ -39,6 +39,17 @@ void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mo
 // Every distinct 4-byte gram of every literal (folded when `fold`), sorted.
 void collect_all_grams(const std::vector<std::vector<Literal>> &literals, bool fold, std::vector<uint32_t> &grams);
 
+// Device form of a combined DFA (see GroupDesc in pm_blob.h).
+struct ScanTable {
+    bool wide = false;
+    int nstates = 0, first_accept = 0, mid_state = 0, stride = 0;
+    std::vector<uint16_t> tab;               // premultiplied next-state entries
+    uint8_t cmap[256] = {0};
+    std::vector<std::vector<int>> accept;    // unit lists of states >= first_accept
+};
+// Returns false if the table does not fit max_bytes in either form.
+bool build_scan_table(const Dfa &d, size_t max_bytes, ScanTable &out);
+
 struct CompiledLibrary {
     std::vector<uint8_t> blob;
     std::vector<PatternInfo> patterns;
@@ -47,6 +58,7 @@ struct CompiledLibrary {
     std::vector<std::vector<Literal>> literals;      // per pattern (empty for tier 2)
     bool fold = false;
     std::vector<Dfa> group_dfas;
+    std::vector<ScanTable> group_scan;
     std::vector<std::vector<int>> group_patterns;    // unit id in a group -> pattern index
     const BlobHeader *header() const { return reinterpret_cast<const BlobHeader *>(blob.data()); }
 };

@@ -529,8 +529,9 @@ int scan_async(pm_batch *b) {
                           w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
         w.launches += 1 + 3 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
-            CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, w.table(), (int)g, w.raw.as<unsigned long long>(), w.raw_cap,
-                               w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
+            const GroupDesc &gd = reinterpret_cast<const GroupDesc *>(b->lib->lib.blob.data() + dl.h.off_groups)[g];
+            CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, w.table(), (int)g, gd.wide != 0, (size_t)gd.nstates * gd.stride * 2,
+                               w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
             w.launches++;
         }
         CU(launch_sort_small(w.raw.as<unsigned long long>(), w.ctr.as<ScanCounters>(), w.raw_cap, w.sort_scratch.as<unsigned long long>(),

@@ -42,6 +42,7 @@ class CompilerHarness:
         self.L.pmt_secondary_match.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t]
         self.L.pmt_stack_match.argtypes = [vp, ctypes.c_char_p, ctypes.c_size_t]
         self.L.pmt_group_match.argtypes = [vp, ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+        self.L.pmt_group_scan_match.argtypes = [vp, ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
         self.L.pmt_filter_triggers.argtypes = [vp, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int]
         self.L.pmt_literals.argtypes = [vp, ctypes.c_int]
         self.L.pmt_unit_states.argtypes = [vp, ctypes.c_int]

@@ -93,6 +93,32 @@ int pmt_group_match(pmt_lib *l, const uint8_t *line, size_t n, int *out, int cap
     return (int)pats.size();
 }
 
+// The same question answered by walking the DEVICE form of the combined DFAs (ScanTable: newline
+// folded into the byte alphabet, premultiplied entries): bytes of the line, then '\n'.
+int pmt_group_scan_match(pmt_lib *l, const uint8_t *line, size_t n, int *out, int cap) {
+    std::vector<int> pats;
+    for (size_t g = 0; g < l->lib.group_scan.size(); g++) {
+        const ScanTable &t = l->lib.group_scan[g];
+        uint32_t s = 0;
+        auto feed = [&](uint8_t b) {
+            s = t.tab[s + (t.wide ? b : t.cmap[b])];
+            uint32_t id = s / t.stride;
+            if ((int)id >= t.first_accept)
+                for (int u : t.accept[id - t.first_accept]) pats.push_back(l->lib.group_patterns[g][u]);
+        };
+        for (size_t i = 0; i < n; i++) feed(line[i]);
+        feed('\n');
+    }
+    std::sort(pats.begin(), pats.end());
+    pats.erase(std::unique(pats.begin(), pats.end()), pats.end());
+    int k = 0;
+    for (int p : pats)
+        if (k < cap) out[k++] = p;
+    return (int)pats.size();
+}
+int pmt_group_is_wide(pmt_lib *l, int g) { return l->lib.group_scan[g].wide; }
+int pmt_group_scan_states(pmt_lib *l, int g) { return l->lib.group_scan[g].nstates; }
+
 // Emulates the gram filter + gram table + literal confirmation on a text whose first byte sits
 // at alignment `phase` (0..3) of the device buffer.  Returns 1 if pattern p would be handed to
 // its verify DFA for this text.

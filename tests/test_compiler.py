@@ -140,6 +140,34 @@ def test_combined_dfa_groups(harness):
         got = sorted(out[i] for i in range(n))
         want = [i for i in tier2 if harness.L.pmt_primary_match(h, i, raw, len(raw))]
         assert got == want, (line[:60], got, want)
+        # the device form of the same automaton (newline folded in, premultiplied rows)
+        n2 = harness.L.pmt_group_scan_match(h, raw, len(raw), out, 128)
+        assert sorted(out[i] for i in range(n2)) == want, (line[:60], want)
+    harness.L.pmt_free(h)
+
+
+def test_scan_table_line_sequences(harness):
+    """The scan table is walked across line boundaries without a reset: feeding several lines
+    back to back (separated by the newline byte) must give each line's own verdict."""
+    rx = [r"^\s+at\s", r"\bOOM\b", r"a$", r"foo\z", r"^ERROR", r"x{3,5}y", r"\d+ms"]
+    rc, h, rep = harness.compile_regexes(rx)
+    assert rc == 0 and rep.n_dfa_scanned == len(rx)
+    out = (ctypes.c_int * 64)()
+    lines = [b"ERROR first", b"  at x", b"not ERROR", b"OOM", b"ZOOM", b"a", b"ab", b"foo", b"xxxy 12ms", b"", b"ERROR"]
+    for i, line in enumerate(lines):
+        prefix = b"\n".join(lines[:i]) + (b"\n" if i else b"")
+        whole = prefix + line
+        # verdict of the last line when walked after all previous ones = verdict of the line alone,
+        # up to the patterns matched by earlier lines (which the walk also reports)
+        n_all = harness.L.pmt_group_scan_match(h, whole, len(whole), out, 64)
+        got_all = set(out[k] for k in range(n_all))
+        n_alone = harness.L.pmt_group_match(h, line, len(line), out, 64)
+        alone = set(out[k] for k in range(n_alone))
+        earlier = set()
+        for prev in lines[:i]:
+            m = harness.L.pmt_group_match(h, prev, len(prev), out, 64)
+            earlier |= set(out[k] for k in range(m))
+        assert got_all == alone | earlier, (i, line, got_all, alone, earlier)
     harness.L.pmt_free(h)
 
 

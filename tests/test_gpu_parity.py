@@ -261,3 +261,18 @@ def test_unsupported_library_is_rejected(engine):
     with pytest.raises(ScanError) as ei:
         engine.compile_library(lib_of(["fine literal here", r"(?<=x)lookbehind"]))
     assert ei.value.status == -3 and ei.value.report["pattern_index"] == 1
+
+
+def test_tier2_dfa_multi_tile(engine):
+    """Patterns without a 7-byte literal go through the combined shared-memory DFA (k_dfa_scan).
+    24 MiB gives every CTA several 64 KiB tiles, so tile carry, speculative entry states and
+    range cuts at line starts are all exercised; LF and CRLF."""
+    regexes = [r"\bGC\b", r"\d{3,}ms", r"^\s+at org\.acme", r"lag=\d+ epoch", r"[Cc]ache (hit|miss)", r"->\s5\d\d", r"id=[0-9a-f]{4}00", r"roles=\[editor\]$",
+               r"(?i)caused by"]
+    lib_json = lib_of(regexes, context_extraction={"lines_before": 1, "lines_after": 1})
+    rep = engine.compile_library(lib_json).report
+    assert rep["n_dfa_scanned"] >= 4 and rep["dfa_groups"] >= 1
+    _, wit, swit = synth.make_library(50)
+    lf = synth.make_corpus(24 << 20, wit, swit, p_hit=1e-3)[0]
+    crlf = synth.make_corpus(3 << 20, wit, swit, p_hit=1e-3, crlf=True, first_line=10 ** 7)[0]
+    check_parity(engine, lib_json, [lf, crlf], expect_events=5000)
