@@ -93,6 +93,8 @@ typedef struct pm_result_view {
     /* first kernel of the scan to the last result copy, one CUDA-event pair per device (includes
      * the host round trip that sizes the sort), max over devices */
     double ms_total;
+    /* the combined-DFA kernel(s) alone (0 when the library has no DFA-scanned pattern) */
+    double ms_dfa;
     /* counters */
     int64_t bytes_scanned, n_candidates, n_verified, gpu_launches;
 } pm_result_view;

@@ -556,34 +556,97 @@ __device__ __forceinline__ uint32_t dfa_next(const DfaCtx &c, uint32_t s, uint32
 }
 
 // '\r' directly in front of a separator '\n' is not part of the line: feed END-OF-LINE ('\n') for it.
-__device__ __forceinline__ uint32_t dfa_cr_fix(const DfaCtx &c, uint32_t b, unsigned long long pos) {
+__device__ __noinline__ uint32_t dfa_cr_fix(const DfaCtx &c, uint32_t b, unsigned long long pos) {
     if (b == '\r' && c.text[pos + 1] == '\n' && !(c.pt.any_trailing_cr && is_pod_raw_end(c.pt, pos + 1))) return '\n';
     return b;
 }
 
-// Walks bytes [lo, hi) of the thread's row; returns the exit state, accumulates the largest state seen.
+// 16 bytes of one 128-bit piece through the DFA.  The per-byte "is this the '\r' of a \r\n" test
+// is hoisted to one SIMD-in-register check per piece; pieces that do hold a '\r' (none in LF
+// logs) take an out-of-line byte loop, which keeps the hot loop small enough for the I-cache.
+__device__ __forceinline__ bool piece_has_cr(const uint4 &v) {
+    uint32_t x0 = v.x ^ 0x0D0D0D0Du, x1 = v.y ^ 0x0D0D0D0Du, x2 = v.z ^ 0x0D0D0D0Du, x3 = v.w ^ 0x0D0D0D0Du;
+    uint32_t z = ((x0 - 0x01010101u) & ~x0) | ((x1 - 0x01010101u) & ~x1) | ((x2 - 0x01010101u) & ~x2) | ((x3 - 0x01010101u) & ~x3);
+    return (z & 0x80808080u) != 0;
+}
+
 template <bool WIDE>
-__device__ __forceinline__ uint32_t dfa_walk(const DfaCtx &c, const uint8_t *buf, int row, int lo, int hi, uint32_t s, uint32_t &smax) {
-    if (lo == 0 && hi == kDfaChunk) {
-#pragma unroll 2
-        for (int k = 0; k < 8; k++) {
-            const uint4 v = *reinterpret_cast<const uint4 *>(buf + row * kDfaChunk + ((k ^ (row & 7)) << 4));
-            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+__device__ __noinline__ void dfa_piece_cr(const DfaCtx &c, uint4 v, unsigned long long pos0, uint32_t &s, uint32_t &smax) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    for (int j = 0; j < 16; j++) {
+        uint32_t b = (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu;
+        if (b == '\r') b = dfa_cr_fix(c, b, pos0 + j);
+        s = dfa_next<WIDE>(c, s, b);
+        smax = max(smax, s);
+    }
+}
+
+template <bool WIDE>
+__device__ __forceinline__ void dfa_piece(const DfaCtx &c, const uint4 &v, unsigned long long pos0, uint32_t &s, uint32_t &smax) {
+    if (piece_has_cr(v)) {
+        dfa_piece_cr<WIDE>(c, v, pos0, s, smax);
+        return;
+    }
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-            for (int j = 0; j < 16; j++) {
-                uint32_t b = (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu;
-                if (b == '\r') b = dfa_cr_fix(c, b, c.tile_start + (unsigned long long)row * kDfaChunk + k * 16 + j);
-                s = dfa_next<WIDE>(c, s, b);
-                smax = max(smax, s);
+    for (int j = 0; j < 16; j++) {
+        const uint32_t b = (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu;
+        s = dfa_next<WIDE>(c, s, b);
+        smax = max(smax, s);
+    }
+}
+
+// Walks bytes [lo, hi) of the thread's row; returns the exit state, accumulates the largest state seen.
+// A full row is walked as TWO independent dependency chains (the lookups are latency-bound): the
+// first half from `s`, the second half from a guessed entry state (mid-line idle state warmed up
+// over the last 32 bytes of the first half).  If the guess differs from the first half's true
+// exit state, the second half is walked again -- same speculation as between rows, resolved
+// inside the thread.
+template <bool WIDE>
+__device__ __forceinline__ uint32_t dfa_walk(const DfaCtx &c, const uint8_t *buf, int row, int lo, int hi, uint32_t s, uint32_t &smax, uint32_t mid_p) {
+    if (lo == 0 && hi == kDfaChunk) {
+        const unsigned long long pos = c.tile_start + (unsigned long long)row * kDfaChunk;
+        const uint8_t *rp = buf + row * kDfaChunk;
+        const int x = row & 7;
+        uint32_t sa = s, sb = mid_p, ma = 0, mb = 0, dummy = 0;
+        // chain B warm-up (pieces 2,3) runs next to chain A's pieces 0,1
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const uint4 va = *reinterpret_cast<const uint4 *>(rp + ((k ^ x) << 4));
+            const uint4 vb = *reinterpret_cast<const uint4 *>(rp + (((k + 2) ^ x) << 4));
+            dfa_piece<WIDE>(c, va, pos + k * 16, sa, ma);
+            dfa_piece<WIDE>(c, vb, pos + (k + 2) * 16, sb, dummy);
+        }
+        const uint32_t guess_b = sb;
+        // chain A: pieces 2,3; chain B: pieces 4,5 -- then B alone: pieces 6,7
+#pragma unroll
+        for (int k = 2; k < 4; k++) {
+            const uint4 va = *reinterpret_cast<const uint4 *>(rp + ((k ^ x) << 4));
+            const uint4 vb = *reinterpret_cast<const uint4 *>(rp + (((k + 2) ^ x) << 4));
+            dfa_piece<WIDE>(c, va, pos + k * 16, sa, ma);
+            dfa_piece<WIDE>(c, vb, pos + (k + 2) * 16, sb, mb);
+        }
+#pragma unroll
+        for (int k = 6; k < 8; k++) {
+            const uint4 vb = *reinterpret_cast<const uint4 *>(rp + ((k ^ x) << 4));
+            dfa_piece<WIDE>(c, vb, pos + k * 16, sb, mb);
+        }
+        if (guess_b != sa) {   // mis-speculated half: walk it again from the truth
+            sb = sa;
+            mb = 0;
+            for (int k = 4; k < 8; k++) {
+                const uint4 vb = *reinterpret_cast<const uint4 *>(rp + ((k ^ x) << 4));
+                dfa_piece<WIDE>(c, vb, pos + k * 16, sb, mb);
             }
         }
-    } else {
-        for (int off = lo; off < hi; off++) {
-            uint32_t b = dfa_tile_byte(buf, row, off);
-            if (b == '\r') b = dfa_cr_fix(c, b, c.tile_start + (unsigned long long)row * kDfaChunk + off);
-            s = dfa_next<WIDE>(c, s, b);
-            smax = max(smax, s);
-        }
+        smax = max(smax, max(ma, mb));
+        return sb;
+    }
+    for (int off = lo; off < hi; off++) {
+        uint32_t b = dfa_tile_byte(buf, row, off);
+        if (b == '\r') b = dfa_cr_fix(c, b, c.tile_start + (unsigned long long)row * kDfaChunk + off);
+        s = dfa_next<WIDE>(c, s, b);
+        smax = max(smax, s);
     }
     return s;
 }
@@ -666,9 +729,9 @@ __global__ void __launch_bounds__(kDfaThreads, 1) k_dfa_scan(const uint8_t *__re
             if (!exact) {
                 uint32_t s = mid_p, dummy = 0;
                 if (lo > 0) {                                // clipped chunk that is not the range start cannot happen; keep it safe
-                    s = dfa_walk<WIDE>(c, buf, tid, max(0, lo - kDfaWarm), lo, s, dummy);
+                    s = dfa_walk<WIDE>(c, buf, tid, max(0, lo - kDfaWarm), lo, s, dummy, mid_p);
                 } else if (tid > 0) {
-                    s = dfa_walk<WIDE>(c, buf, tid - 1, kDfaChunk - kDfaWarm, kDfaChunk, s, dummy);
+                    s = dfa_walk<WIDE>(c, buf, tid - 1, kDfaChunk - kDfaWarm, kDfaChunk, s, dummy, mid_p);
                 } else {                                     // row 0: the bytes in front of it are in the previous tile
                     for (unsigned long long p = cs - kDfaWarm; p < cs; p++) {
                         uint32_t bb = text[p];
@@ -678,7 +741,7 @@ __global__ void __launch_bounds__(kDfaThreads, 1) k_dfa_scan(const uint8_t *__re
                 }
                 guess = s;
             }
-            ex = dfa_walk<WIDE>(c, buf, tid, lo, hi, guess, smax);
+            ex = dfa_walk<WIDE>(c, buf, tid, lo, hi, guess, smax, mid_p);
         }
         // ---- phase B: validate the guesses in chunk order
         const int t0 = (int)((max(c.tile_start, own_lo) - c.tile_start) / kDfaChunk);   // first active row
@@ -695,7 +758,7 @@ __global__ void __launch_bounds__(kDfaThreads, 1) k_dfa_scan(const uint8_t *__re
             if (wrong) {
                 guess = truth;
                 smax = 0;
-                ex = dfa_walk<WIDE>(c, buf, tid, lo, hi, guess, smax);
+                ex = dfa_walk<WIDE>(c, buf, tid, lo, hi, guess, smax, mid_p);
                 exit_s[tid] = (uint16_t)ex;
             }
             __syncthreads();

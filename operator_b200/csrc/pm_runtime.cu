@@ -174,7 +174,7 @@ struct DevWork {
     PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
     cudaStream_t stream = nullptr;
-    cudaEvent_t e[8] = {nullptr};   // 0 h2d0, 1 h2d1, 2 scan0, 3 scan1, 4 mid, 5 post0, 6 post1, 7 d2h1
+    cudaEvent_t e[10] = {nullptr};   // 0 h2d0, 1 h2d1, 2 scan0, 3 scan1, 4 mid, 5 post0, 6 post1, 7 d2h1, 8 dfa0, 9 dfa1
     uint64_t n_events = 0, n_cand = 0, n_verified = 0;
     bool locked = false, staged = false, scanned = false;
     int launches = 0;
@@ -528,12 +528,14 @@ int scan_async(pm_batch *b) {
         CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.tasks.as<unsigned long long>(),
                           w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
         w.launches += 1 + 3 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
+        CU(cudaEventRecord(w.e[8], w.stream));
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
             const GroupDesc &gd = reinterpret_cast<const GroupDesc *>(b->lib->lib.blob.data() + dl.h.off_groups)[g];
             CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, w.table(), (int)g, gd.wide != 0, (size_t)gd.nstates * gd.stride * 2,
                                w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
             w.launches++;
         }
+        CU(cudaEventRecord(w.e[9], w.stream));
         CU(launch_sort_small(w.raw.as<unsigned long long>(), w.ctr.as<ScanCounters>(), w.raw_cap, w.sort_scratch.as<unsigned long long>(),
                              w.uniq.as<unsigned long long>(),
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
@@ -612,7 +614,7 @@ int finish(pm_batch *b, pm_result_view *out) {
     // ---- phase 2: gather in batch pod order
     uint64_t total_events = 0, bytes = 0, n_cand = 0, n_ver = 0;
     int launches = 0;
-    double ms_h2d = 0, ms_scan = 0, ms_post = 0, ms_d2h = 0, ms_total = 0;
+    double ms_h2d = 0, ms_scan = 0, ms_post = 0, ms_d2h = 0, ms_total = 0, ms_dfa = 0;
     for (auto &w : b->work) {
         CU(cudaSetDevice(ctx->devs[w.slot]->id));
         CU(cudaStreamSynchronize(w.stream));
@@ -630,6 +632,9 @@ int finish(pm_batch *b, pm_result_view *out) {
         cudaEventElapsedTime(&dd, w.e[6], w.e[7]);
         cudaEventElapsedTime(&tt, w.e[2], w.e[7]);
         ms_total = std::max<double>(ms_total, tt);
+        float df = 0;
+        cudaEventElapsedTime(&df, w.e[8], w.e[9]);
+        if (b->lib->dev[w.slot].h.n_groups) ms_dfa = std::max<double>(ms_dfa, df);
         ms_h2d = std::max<double>(ms_h2d, a);
         ms_scan = std::max<double>(ms_scan, s);
         ms_post = std::max<double>(ms_post, p1 + p2);
@@ -713,6 +718,7 @@ int finish(pm_batch *b, pm_result_view *out) {
     v.ms_post = ms_post;
     v.ms_d2h = ms_d2h;
     v.ms_total = ms_total;
+    v.ms_dfa = ms_dfa;
     v.bytes_scanned = (int64_t)bytes;
     v.n_candidates = (int64_t)n_cand;
     v.n_verified = (int64_t)n_ver;

@@ -51,7 +51,7 @@ class ResultView(ctypes.Structure):
                 ("ctx_first_line", _P(ctypes.c_int32)), ("ctx_last_line", _P(ctypes.c_int32)),
                 ("ctx_start", _P(ctypes.c_int64)), ("ctx_end", _P(ctypes.c_int64)), ("score", _P(ctypes.c_double)),
                 ("pod_tag", _P(ctypes.c_uint64)), ("pod_first_event", _P(ctypes.c_int64)), ("pod_n_lines", _P(ctypes.c_int32)),
-                ("ms_h2d", ctypes.c_double), ("ms_scan", ctypes.c_double), ("ms_post", ctypes.c_double), ("ms_d2h", ctypes.c_double), ("ms_total", ctypes.c_double),
+                ("ms_h2d", ctypes.c_double), ("ms_scan", ctypes.c_double), ("ms_post", ctypes.c_double), ("ms_d2h", ctypes.c_double), ("ms_total", ctypes.c_double), ("ms_dfa", ctypes.c_double),
                 ("bytes_scanned", ctypes.c_int64), ("n_candidates", ctypes.c_int64), ("n_verified", ctypes.c_int64),
                 ("gpu_launches", ctypes.c_int64)]
 
@@ -149,6 +149,7 @@ class Result:
         self.pod_first_event = c(_arr(v.pod_first_event, p + 1, np.int64))
         self.pod_n_lines = c(_arr(v.pod_n_lines, p, np.int32))
         self.ms_h2d, self.ms_scan, self.ms_post, self.ms_d2h, self.ms_total = v.ms_h2d, v.ms_scan, v.ms_post, v.ms_d2h, v.ms_total
+        self.ms_dfa = v.ms_dfa
         self.bytes_scanned, self.n_candidates, self.n_verified = int(v.bytes_scanned), int(v.n_candidates), int(v.n_verified)
         self.gpu_launches = int(v.gpu_launches)
 
