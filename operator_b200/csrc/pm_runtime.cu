@@ -182,6 +182,13 @@ struct DevWork {
 
 size_t round_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// PM_TEST_TINY_QUEUES=1 starts every internal queue (filter candidates, raw events, resolve work
+// items) at a few entries, so that the overflow -> grow -> rerun paths run on small test inputs.
+bool tiny_queues() {
+    static const bool v = getenv("PM_TEST_TINY_QUEUES") != nullptr;
+    return v;
+}
+
 // Length without trailing "\r?\n" separators (Java split drops trailing empty strings).
 size_t effective_len(const uint8_t *p, size_t n) {
     while (n > 0 && p[n - 1] == '\n') {
@@ -338,6 +345,7 @@ int stage(pm_batch *b) {
         if (w.total >= (1ull << 40)) return fail(PM_E_INVALID, "more than 1 TiB of log text on one device");
         w.cand_cap = std::max<uint64_t>(1u << 20, w.total / 256);
         w.raw_cap = std::max<uint64_t>(1u << 18, w.total / 1024);
+        if (tiny_queues()) w.cand_cap = 64, w.raw_cap = 32;
         if ((rc = get(d->pool, w.total, w.text))) return rc;
         if ((rc = get(d->pool, w.n_tiles * 4, w.tile_nl))) return rc;
         if ((rc = get(d->pool, w.n_tiles * 8, w.tile_prefix))) return rc;
@@ -470,7 +478,7 @@ int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
     Device *d = ctx->devs[w.slot];
     if (ev_cap < w.ev_cap) ev_cap = w.ev_cap;
     w.ev_cap = ev_cap;
-    w.item_cap = std::min<uint64_t>(std::max<uint64_t>(w.item_cap, ev_cap * 96 + (1u << 16)), 0xFFFFFFF0ull);
+    w.item_cap = std::min<uint64_t>(std::max<uint64_t>(w.item_cap, tiny_queues() ? 16 : ev_cap * 96 + (1u << 16)), 0xFFFFFFF0ull);
     w.long_cap = std::max<uint64_t>(w.long_cap, w.item_cap / 8 + (1u << 12));
     SoaLayout L(ev_cap);
     int rc;

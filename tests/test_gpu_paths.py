@@ -1,0 +1,100 @@
+"""GPU tests of the less-travelled paths: queue overflow -> rerun, the radix-sort path for many
+raw events, the 20k-pattern library (BASELINE config 4 shape), many small pods (config 3 shape)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import oracle, pcre2_oracle
+from operator_b200 import synth
+from tests.test_gpu_parity import check_parity, lib_of, _got
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+_TINY = r"""
+import sys
+sys.path.insert(0, %r)
+from operator_b200 import Engine, synth
+from oracle import oracle
+lib_json, wit, swit = synth.make_library(50)
+corpus, _ = synth.make_corpus(600000, wit, swit, p_hit=5e-2)
+eng = Engine(1)
+eng.compile_library(lib_json).publish()
+for rounds in range(2):                      # second scan reuses grown queues from the pool
+    res = eng.scan([corpus, corpus[:200000]])
+    for pod, log in enumerate([bytes(corpus), bytes(corpus[:200000])]):
+        want = [(e.line_no, e.pattern, e.ctx_first, e.ctx_last, e.score) for e in oracle.analyze(log, oracle.load_library(lib_json))]
+        got = [(g["line_no"], g["pattern"], g["ctx_first"], g["ctx_last"], g["score"]) for g in res.events_of(pod)]
+        assert got == want and len(want) > 50, (pod, len(got), len(want))
+eng.close()
+print("tiny-queues ok")
+"""
+
+
+def test_overflow_rerun_paths(tmp_path):
+    """Every internal queue starts at a few entries (PM_TEST_TINY_QUEUES): candidate queue, raw
+    events, verify tasks and resolve work items all overflow and are grown, results stay exact."""
+    script = tmp_path / "tiny.py"
+    script.write_text(_TINY % ROOT)
+    env = dict(os.environ, PM_TEST_TINY_QUEUES="1")
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "tiny-queues ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+def test_many_raw_events_take_the_radix_sort_path(engine):
+    """More than 16384 raw events: the one-CTA sort declines, the host-sized radix sort runs."""
+    lib_json, wit, swit = synth.make_library(50)
+    corpus, n_lines = synth.make_corpus(12 << 20, wit, swit, p_hit=0.25)
+    res = check_parity(engine, lib_json, [corpus], expect_events=17000)
+    assert res.n_events > 16384
+
+
+@pytest.mark.skipif(not pcre2_oracle.available(), reason="libpcre2-8 not loadable")
+def test_large_library_20k_patterns(engine):
+    """BASELINE config 4 shape: 20 000 patterns.  (line, pattern) pairs against PCRE2 over the whole
+    sample, full event parity against the Python oracle on the head of it."""
+    lib_json, wit, swit = synth.make_library(20000)
+    rep = engine.compile_library(lib_json).publish().report
+    assert rep["n_patterns"] == 20000
+    corpus, n_lines = synth.make_corpus(300000, wit, swit, p_hit=5e-2)
+    res = engine.scan([corpus])
+    pl = pcre2_oracle.Pcre2Library([p["primary_pattern"]["regex"] for p in lib_json["patterns"]])
+    starts, lens = pcre2_oracle.split(corpus)
+    ol, op, total = pcre2_oracle.scan(pl, corpus, starts, lens, threads=os.cpu_count() or 4)
+    want = sorted(zip((ol + 1).tolist(), op.tolist()))
+    got = sorted(zip(res.line_no.tolist(), res.pattern_index.tolist()))
+    assert got == want and len(want) > 50
+    head = bytes(corpus[:20000])
+    head = head[:head.rfind(b"\n") + 1]
+    olib = oracle.load_library(lib_json)
+    ev = oracle.analyze(head, olib)
+    got_head = [t for t in _got(res, 0) if t[2] < len(head)]
+    assert [t[:2] for t in got_head] == [(e.line_no, e.pattern) for e in ev]
+    assert [t[8] for t in got_head] == [e.score for e in ev]
+
+
+def test_crash_storm_many_small_pods(engine):
+    """BASELINE config 3 shape, scaled down: 3000 pods in one batch; every pod keeps its own line
+    numbering and context clipping.  Parity on a seeded sample of 64 pods."""
+    lib_json, wit, swit = synth.make_library(50)
+    engine.compile_library(lib_json).publish()
+    olib = oracle.load_library(lib_json)
+    big, _ = synth.make_corpus(24 << 20, wit, swit, p_hit=2e-2)
+    nl = np.flatnonzero(big == 10)
+    pods, pos = [], 0
+    rng = np.random.default_rng(7)
+    for k in range(3000):
+        n = int(rng.integers(5, 120))
+        hi = nl[min(len(nl) - 1, np.searchsorted(nl, pos) + n)] + 1
+        pods.append(big[pos:hi] if k % 7 else big[pos:hi - 1])      # some pods lack the final newline
+        pos = hi
+    res = engine.scan(pods)
+    assert res.n_pods == 3000 and res.n_events > 1000
+    for k in rng.choice(3000, 64, replace=False):
+        want = [(e.line_no, e.pattern, e.line_start, e.line_len, e.ctx_first, e.ctx_last, e.ctx_start, e.ctx_end, e.score)
+                for e in oracle.analyze(bytes(pods[k]), olib)]
+        assert _got(res, int(k)) == want, k
+        assert int(res.pod_n_lines[k]) == len(oracle.split_lines(bytes(pods[k])))
