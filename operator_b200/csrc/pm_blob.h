@@ -89,7 +89,13 @@ struct GroupDesc {
 };
 
 constexpr uint32_t kFilterMult0 = 0x9E3779B1u;   // default multiplier; the runtime may reseed (pm_runtime.cu)
-PM_HD uint32_t gram_filter_bit(uint32_t gram, uint32_t log2_bits, uint32_t mult = kFilterMult0) { return (gram * mult) >> (32u - log2_bits); }
+// First-level filter bit of a gram: the bitmap WORD comes from the top (log2_bits - 5) bits of the
+// multiplicative hash, the bit inside the word from the hash's low 5 bits (k_scan tests it with
+// one wrapping shift, no extra instruction to extract the bit index).
+PM_HD uint32_t gram_filter_bit(uint32_t gram, uint32_t log2_bits, uint32_t mult = kFilterMult0) {
+    const uint32_t h = gram * mult;
+    return ((h >> (37u - log2_bits)) << 5) | (h & 31u);
+}
 PM_HD uint32_t gram_filter_bit2(uint32_t gram, uint32_t log2_bits2) { return (gram * 0xC2B2AE3Du) >> (32u - log2_bits2); }
 PM_HD uint32_t gram_table_slot(uint32_t gram, uint32_t log2_cap) { return (gram * 0x85EBCA6Bu) >> (32u - log2_cap); }
 

@@ -68,18 +68,79 @@ __device__ __forceinline__ unsigned lanemask_lt() {
 }
 
 // ------------------------------------------------------------------------------------ k_scan
-template <int BITS, bool FOLD>
-__device__ __forceinline__ uint32_t filter_word(uint32_t w, const uint32_t *bm) {
-    uint32_t g = FOLD ? (w | 0x20202020u) : w;
-    uint32_t bit = (g * kFilterMult0) >> (32 - BITS);
-    return (bm[bit >> 5] >> (bit & 31u)) & 1u;
+// ---- hot-loop primitives.  ncu (profiles/r01_*) showed the first version of this loop bound by
+// the ALU pipe (LOP3/SHF/IADD: 69 % of its instructions, pipe ~89 % busy) while the FMA pipe,
+// which executes IMAD, idled.  The loop below therefore expresses shifts and adds as integer
+// multiply-adds wherever that is exact and never materialises a bit index.  The constants arrive
+// as a kernel parameter (constant bank) on purpose: ptxas folds literal powers of two back into
+// LEA/VIADD/SHF, i.e. back onto the ALU pipe.
+//   (w ^ 0x0A..) & 0x7F..            one LOP3 (register constants)
+//   t + 0x7F..                       IMAD  t * 1 + c           (FMA pipe)
+//   (u | w) & 0x80..                 one LOP3  -> bit 7 of each byte: "not a newline"
+//   per-byte counters += flags >> 7  IMAD.HI  hi(f * 2^25) + acc (FMA pipe), 4 counters per register
+//   bitmap word index                IMAD.HI  hi(h * 2^(BITS-5))   (top bits of the hash)
+//   shared address                   IMAD     idx * 4 + base
+//   bit test                         SHF.R.W  word >> (h & 31): the shifter wraps, no extraction
+__device__ __forceinline__ uint32_t lop3_xor_and(uint32_t a, uint32_t b, uint32_t c) {   // (a ^ b) & c
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0x28;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t lop3_or_and(uint32_t a, uint32_t b, uint32_t c) {    // (a | b) & c
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xA8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t lop3_or3(uint32_t a, uint32_t b, uint32_t c) {       // a | b | c
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xFE;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t mad_hi(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t shr_wrap(uint32_t v, uint32_t amount) {              // v >> (amount & 31)
+    uint32_t r;
+    asm("shf.r.wrap.b32 %0, %1, 0, %2;" : "=r"(r) : "r"(v), "r"(amount));
+    return r;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+    uint32_t r;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(saddr));
+    return r;
+}
+
+struct ScanConsts {
+    uint32_t c_nl, c_7f, c_80, c_20, one, four, two25, idx_mul, mult, bm_base;
+};
+
+// One aligned text word: updates the per-byte "not newline" counters, returns the word's filter
+// bit in bit 0 of the result (other bits are garbage).
+template <bool FOLD>
+__device__ __forceinline__ uint32_t scan_word(uint32_t w, const ScanConsts &k, uint32_t &nz_acc) {
+    const uint32_t t = lop3_xor_and(w, k.c_nl, k.c_7f);
+    const uint32_t u = mad_lo(t, k.one, k.c_7f);
+    const uint32_t f = lop3_or_and(u, w, k.c_80);
+    nz_acc = mad_hi(f, k.two25, nz_acc);
+    const uint32_t g = FOLD ? (w | k.c_20) : w;
+    const uint32_t h = g * k.mult;
+    const uint32_t idx = mad_hi(h, k.idx_mul, 0u);
+    const uint32_t word = lds_u32(mad_lo(idx, k.four, k.bm_base));
+    return shr_wrap(word, h);
 }
 
 template <int BITS, bool FOLD>
 __global__ void __launch_bounds__(kScanThreads, 1)
 k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g, const uint4 *__restrict__ bitmap2_g,
        uint32_t bits2, uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
-       ScanCounters *__restrict__ ctr) {
+       ScanCounters *__restrict__ ctr, const ScanConsts kc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int kBitmapWords = (1 << BITS) / 32;
     uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);
@@ -99,58 +160,73 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
     const unsigned long long n_warps = (unsigned long long)gridDim.x * (kScanThreads / 32);
     const unsigned lt = lanemask_lt();
     const unsigned long long pol = l2_evict_first_policy();
+    ScanConsts k = kc;
+    k.bm_base = (uint32_t)__cvta_generic_to_shared(bm);
 
-    for (unsigned long long t = (unsigned long long)blockIdx.x * (kScanThreads / 32) + warp; t < n_tiles; t += n_warps) {
-        const uint4 *base = text + t * (kTileBytes / 16) + lane;
-        uint4 v[4];
+    // software pipeline: the next tile's four 128-bit loads are in flight while this tile is
+    // processed (a warp alone would otherwise alternate "wait ~1 us for HBM" and "compute")
+    unsigned long long t = (unsigned long long)blockIdx.x * (kScanThreads / 32) + warp;
+    uint4 v[4];
+    if (t < n_tiles) {
 #pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = ld_stream16_ef(base + j * 32, pol);   // 4 x 512 B per warp in flight
-        uint32_t nz = 0;
+        for (int j = 0; j < 4; j++) v[j] = ld_stream16_ef(text + t * (kTileBytes / 16) + lane + j * 32, pol);
+    }
+    for (; t < n_tiles; t += n_warps) {
+        uint4 nx[4];
+        {
+            const unsigned long long tn = t + n_warps < n_tiles ? t + n_warps : t;   // last round: harmless re-load
+            const uint4 *nb = text + tn * (kTileBytes / 16) + lane;
+#pragma unroll
+            for (int j = 0; j < 4; j++) nx[j] = ld_stream16_ef(nb + j * 32, pol);
+        }
+        uint32_t nz_acc = 0;   // four byte-wide counters of non-newline bytes (<= 16 each per tile)
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            uint32_t f0 = not_newline_flags(v[j].x), f1 = not_newline_flags(v[j].y);
-            uint32_t f2 = not_newline_flags(v[j].z), f3 = not_newline_flags(v[j].w);
-            nz += __popc(f0 | (f1 >> 1) | (f2 >> 2) | (f3 >> 3));
-            uint32_t m4 = filter_word<BITS, FOLD>(v[j].x, bm) | (filter_word<BITS, FOLD>(v[j].y, bm) << 1) |
-                          (filter_word<BITS, FOLD>(v[j].z, bm) << 2) | (filter_word<BITS, FOLD>(v[j].w, bm) << 3);
-            unsigned b = __ballot_sync(FULL, m4 != 0);
+            const uint32_t t0 = scan_word<FOLD>(v[j].x, k, nz_acc), t1 = scan_word<FOLD>(v[j].y, k, nz_acc);
+            const uint32_t t2 = scan_word<FOLD>(v[j].z, k, nz_acc), t3 = scan_word<FOLD>(v[j].w, k, nz_acc);
+            const uint32_t any = lop3_or_and(lop3_or3(t0, t1, t2), t3, k.one);
+            unsigned b = __ballot_sync(FULL, any != 0);
             if (b) {   // warp-uniform, rare.  Second-level filter first: an independent hash into a small
                        // bitmap removes the first level's collisions before anything is queued
+                uint32_t m4 = (t0 & 1u) | ((t1 & 1u) << 1) | ((t2 & 1u) << 2) | ((t3 & 1u) << 3);
                 if (m4) {
                     const uint32_t w4[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
 #pragma unroll
-                    for (int k = 0; k < 4; k++)
-                        if (m4 & (1u << k)) {
-                            uint32_t g = FOLD ? (w4[k] | 0x20202020u) : w4[k];
+                    for (int q = 0; q < 4; q++)
+                        if (m4 & (1u << q)) {
+                            uint32_t g = FOLD ? (w4[q] | 0x20202020u) : w4[q];
                             uint32_t bit2 = (g * 0xC2B2AE3Du) >> shift2;
-                            if (!((bm2[bit2 >> 5] >> (bit2 & 31u)) & 1u)) m4 &= ~(1u << k);
+                            if (!((bm2[bit2 >> 5] >> (bit2 & 31u)) & 1u)) m4 &= ~(1u << q);
                         }
                 }
                 b = __ballot_sync(FULL, m4 != 0);
-            }
-            if (b) {   // stage (group, mask) entries, flush 32 at a time
-                if (m4) wq[qn + __popc(b & lt)] = ((t * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
-                qn += __popc(b);
-                __syncwarp();
-                if (qn >= 32) {
-                    unsigned long long at = 0;
-                    if (lane == 0) at = atomicAdd(&ctr->n_cand, 32ull);
-                    at = __shfl_sync(FULL, at, 0);
-                    if (at + 32 <= cand_cap)
-                        cand[at + lane] = wq[lane];
-                    else if (lane == 0)
-                        ctr->cand_overflow = 1;
-                    unsigned long long carry = (lane + 32 < qn) ? wq[lane + 32] : 0ull;
+                if (b) {   // stage (group, mask) entries, flush 32 at a time
+                    if (m4) wq[qn + __popc(b & lt)] = ((t * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
+                    qn += __popc(b);
                     __syncwarp();
-                    qn -= 32;
-                    if (lane < qn) wq[lane] = carry;
-                    __syncwarp();
+                    if (qn >= 32) {
+                        unsigned long long at = 0;
+                        if (lane == 0) at = atomicAdd(&ctr->n_cand, 32ull);
+                        at = __shfl_sync(FULL, at, 0);
+                        if (at + 32 <= cand_cap)
+                            cand[at + lane] = wq[lane];
+                        else if (lane == 0)
+                            ctr->cand_overflow = 1;
+                        unsigned long long carry = (lane + 32 < qn) ? wq[lane + 32] : 0ull;
+                        __syncwarp();
+                        qn -= 32;
+                        if (lane < qn) wq[lane] = carry;
+                        __syncwarp();
+                    }
                 }
             }
         }
-        // 16 bytes x 4 loads per lane: newlines = 64 - non-newline bytes
+        // horizontal sum of the four byte counters, then newlines = 64 - non-newline bytes
+        const uint32_t nz = (nz_acc * 0x01010101u) >> 24;
         uint32_t nl = __reduce_add_sync(FULL, 64u - nz);
         if (lane == 0) tile_nl[t] = nl;
+#pragma unroll
+        for (int j = 0; j < 4; j++) v[j] = nx[j];
     }
     if (qn > 0) {
         unsigned long long at = 0;
@@ -1268,14 +1344,25 @@ cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long 
                              unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
     size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(1u << bits2) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
     cudaError_t e;
+    ScanConsts kc;
+    kc.c_nl = 0x0A0A0A0Au;
+    kc.c_7f = 0x7F7F7F7Fu;
+    kc.c_80 = 0x80808080u;
+    kc.c_20 = 0x20202020u;
+    kc.one = 1u;
+    kc.four = 4u;
+    kc.two25 = 1u << 25;
+    kc.idx_mul = 1u << (BITS - 5);
+    kc.mult = kFilterMult0;
+    kc.bm_base = 0;
     if (fold) {
         e = cudaFuncSetAttribute(k_scan<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, kc);
     } else {
         e = cudaFuncSetAttribute(k_scan<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr);
+        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, kc);
     }
     return cudaGetLastError();
 }
