@@ -77,7 +77,7 @@ __device__ __forceinline__ unsigned lanemask_lt() {
 //   (w ^ 0x0A..) & 0x7F..            one LOP3 (register constants)
 //   t + 0x7F..                       IMAD  t * 1 + c           (FMA pipe)
 //   (u | w) & 0x80..                 one LOP3  -> bit 7 of each byte: "not a newline"
-//   per-byte counters += flags >> 7  IMAD.HI  hi(f * 2^25) + acc (FMA pipe), 4 counters per register
+//   counter += 0x80 * popcount       IDP.4A   dot(f, 0x01010101) + acc (one instruction, no shift/popc)
 //   bitmap word index                IMAD.HI  hi(h * 2^(BITS-5))   (top bits of the hash)
 //   shared address                   IMAD     idx * 4 + base
 //   bit test                         SHF.R.W  word >> (h & 31): the shifter wraps, no extraction
@@ -128,7 +128,7 @@ __device__ __forceinline__ uint32_t scan_word(uint32_t w, const ScanConsts &k, u
     const uint32_t t = lop3_xor_and(w, k.c_nl, k.c_7f);
     const uint32_t u = mad_lo(t, k.one, k.c_7f);
     const uint32_t f = lop3_or_and(u, w, k.c_80);
-    nz_acc = mad_hi(f, k.two25, nz_acc);
+    nz_acc = __dp4a(f, k.two25, nz_acc);   // += 0x80 * (number of non-newline bytes); k.two25 holds 0x01010101
     const uint32_t g = FOLD ? (w | k.c_20) : w;
     const uint32_t h = g * k.mult;
     const uint32_t idx = mad_hi(h, k.idx_mul, 0u);
@@ -165,21 +165,8 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
 
     // software pipeline: the next tile's four 128-bit loads are in flight while this tile is
     // processed (a warp alone would otherwise alternate "wait ~1 us for HBM" and "compute")
-    unsigned long long t = (unsigned long long)blockIdx.x * (kScanThreads / 32) + warp;
-    uint4 v[4];
-    if (t < n_tiles) {
-#pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = ld_stream16_ef(text + t * (kTileBytes / 16) + lane + j * 32, pol);
-    }
-    for (; t < n_tiles; t += n_warps) {
-        uint4 nx[4];
-        {
-            const unsigned long long tn = t + n_warps < n_tiles ? t + n_warps : t;   // last round: harmless re-load
-            const uint4 *nb = text + tn * (kTileBytes / 16) + lane;
-#pragma unroll
-            for (int j = 0; j < 4; j++) nx[j] = ld_stream16_ef(nb + j * 32, pol);
-        }
-        uint32_t nz_acc = 0;   // four byte-wide counters of non-newline bytes (<= 16 each per tile)
+    auto process_tile = [&](unsigned long long tt, uint4 (&v)[4]) {
+        uint32_t nz_acc = 0;   // 0x80 per non-newline byte of this lane's 64 bytes
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             const uint32_t t0 = scan_word<FOLD>(v[j].x, k, nz_acc), t1 = scan_word<FOLD>(v[j].y, k, nz_acc);
@@ -201,7 +188,7 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
                 }
                 b = __ballot_sync(FULL, m4 != 0);
                 if (b) {   // stage (group, mask) entries, flush 32 at a time
-                    if (m4) wq[qn + __popc(b & lt)] = ((t * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
+                    if (m4) wq[qn + __popc(b & lt)] = ((tt * (kTileBytes / 16) + j * 32 + lane) << 4) | m4;
                     qn += __popc(b);
                     __syncwarp();
                     if (qn >= 32) {
@@ -222,11 +209,28 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
             }
         }
         // horizontal sum of the four byte counters, then newlines = 64 - non-newline bytes
-        const uint32_t nz = (nz_acc * 0x01010101u) >> 24;
+        const uint32_t nz = nz_acc >> 7;
         uint32_t nl = __reduce_add_sync(FULL, 64u - nz);
-        if (lane == 0) tile_nl[t] = nl;
+        if (lane == 0) tile_nl[tt] = nl;
+    };
+    // ping-pong between two register sets so that no copy is needed between rounds
+    unsigned long long t = (unsigned long long)blockIdx.x * (kScanThreads / 32) + warp;
+    uint4 va[4], vb[4];
+    auto load_tile = [&](unsigned long long tt, uint4 (&dst)[4]) {
+        const unsigned long long tc = tt < n_tiles ? tt : n_tiles - 1;   // past the end: harmless re-load
+        const uint4 *nb = text + tc * (kTileBytes / 16) + lane;
 #pragma unroll
-        for (int j = 0; j < 4; j++) v[j] = nx[j];
+        for (int j = 0; j < 4; j++) dst[j] = ld_stream16_ef(nb + j * 32, pol);
+    };
+    if (t < n_tiles) load_tile(t, va);
+    while (t < n_tiles) {
+        load_tile(t + n_warps, vb);
+        process_tile(t, va);
+        t += n_warps;
+        if (t >= n_tiles) break;
+        load_tile(t + n_warps, va);
+        process_tile(t, vb);
+        t += n_warps;
     }
     if (qn > 0) {
         unsigned long long at = 0;
@@ -1351,7 +1355,7 @@ cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long 
     kc.c_20 = 0x20202020u;
     kc.one = 1u;
     kc.four = 4u;
-    kc.two25 = 1u << 25;
+    kc.two25 = 0x01010101u;   // dp4a weights
     kc.idx_mul = 1u << (BITS - 5);
     kc.mult = kFilterMult0;
     kc.bm_base = 0;

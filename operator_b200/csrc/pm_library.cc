@@ -240,7 +240,7 @@ void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mo
     out.log2_cap = 4;
     if (out.n_grams) {
         out.log2_bits = 15;
-        while (out.log2_bits < 20 && (1ull << out.log2_bits) < 512ull * out.n_grams) out.log2_bits++;
+        while (out.log2_bits < 20 && (1ull << out.log2_bits) < 1024ull * out.n_grams) out.log2_bits++;
         while ((1u << out.log2_cap) < 2 * out.n_grams) out.log2_cap++;
     }
     out.log2_bits2 = out.log2_bits ? std::min<uint32_t>(out.log2_bits, 18) : 0;
