@@ -292,6 +292,8 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         std::vector<SecDesc> sdesc;
         std::vector<Dfa> &units = out.unit_dfas;
         std::vector<NodePtr> asts;
+        std::map<std::string, uint32_t> sec_units;   // secondary regex source -> unit
+        std::vector<uint32_t> context_units;         // units walked by the resolve stage (secondaries, STACK)
 
         for (const JsonValue *lib : libs) {
             if (lib->type != JsonValue::Object) throw CompileFail{PM_E_SYNTAX, -1, -1, -1, "", "library must be a JSON object"};
@@ -359,9 +361,17 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
                         if (num_of(s.get("proximity_window"), v)) sd.window = (int32_t)v;
                         if (sd.window < 0 || sd.window > 1000)
                             throw CompileFail{PM_E_SYNTAX, idx, j, -1, pi.id, "proximity_window out of range"};
-                        sd.unit = (uint32_t)units.size();
-                        units.emplace_back();
-                        compile_unit(srx->str, idx, j, pi.id, units.back(), nullptr);
+                        // identical secondary regexes share one unit (one table, hot in L1/L2)
+                        auto cached = sec_units.find(srx->str);
+                        if (cached != sec_units.end()) {
+                            sd.unit = cached->second;
+                        } else {
+                            sd.unit = (uint32_t)units.size();
+                            units.emplace_back();
+                            compile_unit(srx->str, idx, j, pi.id, units.back(), nullptr);
+                            sec_units.emplace(srx->str, sd.unit);
+                            context_units.push_back(sd.unit);
+                        }
                         sdesc.push_back(sd);
                         j++;
                     }
@@ -391,6 +401,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         uint32_t stack_unit = (uint32_t)units.size();
         units.emplace_back();
         compile_unit(kStackRegex, -1, -1, "<stack>", units.back(), nullptr);
+        context_units.push_back(stack_unit);
 
         // ---- tiering: literal-gram filter where a 7+ byte literal is required, DFA otherwise
         out.literals.resize(P);
@@ -428,13 +439,28 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         Section units_sec, classmaps, tables, groups_sec, gaccept;
         auto put_dfa = [&](const Dfa &d, uint32_t &table_off, uint32_t &cm_off) {
             cm_off = (uint32_t)classmaps.push_raw(d.classmap, 256);
+            while (tables.bytes.size() % 16) tables.bytes.push_back(0);   // 16-byte aligned: vector copies into shared memory
             table_off = (uint32_t)(tables.bytes.size() / 2);
             tables.push_raw(d.next.data(), d.next.size() * 2);
         };
-        for (auto &d : units) {
+        std::vector<char> is_context(units.size(), 0);
+        for (uint32_t cu : context_units) is_context[cu] = 1;
+        size_t wide_budget = 16u << 20;
+        for (size_t ui = 0; ui < units.size(); ui++) {
+            const Dfa &d = units[ui];
             UnitDesc u;
             memset(&u, 0, sizeof u);
             put_dfa(d, u.table_off, u.classmap_off);
+            u.wide_off = 0xFFFFFFFFu;
+            if (is_context[ui] && (size_t)d.nstates * 512 <= wide_budget) {
+                wide_budget -= (size_t)d.nstates * 512;
+                while (tables.bytes.size() % 16) tables.bytes.push_back(0);
+                u.wide_off = (uint32_t)(tables.bytes.size() / 2);
+                std::vector<uint16_t> wide((size_t)d.nstates * 256);
+                for (int q = 0; q < d.nstates; q++)
+                    for (int b = 0; b < 256; b++) wide[(size_t)q * 256 + b] = d.next[(size_t)q * d.stride() + d.classmap[b]];
+                tables.push_raw(wide.data(), wide.size() * 2);
+            }
             u.nstates = (uint16_t)d.nstates;
             u.stride = (uint16_t)d.stride();
             u.accept_state = (uint16_t)d.first_accept;   // early-accept: one sticky state
