@@ -32,8 +32,8 @@ sys.path.insert(0, ROOT)
 CORPUS_BYTES = 1 << 30
 N_PATTERNS = 500
 P_HIT = 1e-3
-CPU_SAMPLE_BYTES = 64 << 20
-REF_STEP_BYTES = 16 << 20
+CPU_SAMPLE_BYTES = 1 << 30      # the whole config-2 corpus: ~15 s on 16 cores, no extrapolation needed
+REF_STEP_BYTES = 64 << 20
 
 
 def parse_args():
@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--corpus-bytes", type=int, default=CORPUS_BYTES)
     ap.add_argument("--patterns", type=int, default=N_PATTERNS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true")
     return ap.parse_args()
 
 
@@ -238,6 +239,49 @@ def main():
     sampler.mark()
     sampler.stop()
 
+    # ---- pattern-count sweep (the metric is "GB/s vs pattern count"): same corpus, nested libraries
+    sweep = []
+    if world == 1 and not args.no_sweep:
+        for n_pat in (50, 5000, 20000):
+            lj, _, _ = synth.make_library(n_pat)
+            t0 = time.perf_counter()
+            rep = eng.compile_library(lj).publish().report
+            compile_s = time.perf_counter() - t0
+            sb = eng.batch()
+            sb.add_pod(corpus, 0)
+            sb.stage()
+            for _ in range(4):          # includes the one-off filter adaptation
+                sr = sb.rescan(copy=False)
+            ms_t = ms_s = 0.0
+            for _ in range(5):
+                sr = sb.rescan(copy=False)
+                ms_t += sr.ms_total
+                ms_s += sr.ms_scan
+            sweep.append({"patterns": n_pat, "k_scan_gbs": nbytes / (ms_s / 5 * 1e-3) / 1e9, "step_gbs": nbytes / (ms_t / 5 * 1e-3) / 1e9,
+                          "frac_of_measured_hbm": nbytes / (ms_s / 5 * 1e-3) / 1e9 / peak_hbm()[0], "events": int(sr.n_events),
+                          "filter_candidates": int(sr.n_candidates), "library_blob_bytes": rep["blob_bytes"], "compile_s": round(compile_s, 2)})
+            sb.release()
+        eng.compile_library(lib_json).publish()
+
+    # ---- BASELINE config 1: one ~10k-line pod log vs the ~50-pattern library, end-to-end latency
+    latency = None
+    if world == 1 and not args.no_sweep:
+        lj, w50, s50 = synth.make_library(50)
+        eng.compile_library(lj).publish()
+        small, small_lines = synth.make_corpus(1400 << 10, w50, s50, p_hit=1e-3)
+        small_pinned = eng.pinned(int(small.size))
+        small_pinned.array[:small.size] = small
+        for _ in range(5):
+            eng.scan([small_pinned.array[:small.size]])
+        t0 = time.perf_counter()
+        for _ in range(50):
+            lr = eng.scan([small_pinned.array[:small.size]])
+        latency = {"workload": "configs[0]: one pod log, %d lines, %d bytes, 50 patterns" % (small_lines, small.size),
+                   "ms_end_to_end": (time.perf_counter() - t0) / 50 * 1e3, "ms_h2d": lr.ms_h2d, "ms_k_scan": lr.ms_scan, "ms_device_total": lr.ms_total,
+                   "events": int(lr.n_events), "note": "launch/latency-bound at this size: a roofline fraction is not meaningful"}
+        small_pinned.free()
+        eng.compile_library(lib_json).publish()
+
     # ---- reductions: max time over ranks, sum of bytes
     step_ms = dist.max_over_ranks(ms_total / args.steps, dev)
     scan_ms = dist.max_over_ranks(ms_scan / args.steps, dev)
@@ -273,6 +317,8 @@ def main():
                          "whole_step_frac": (nbytes / (step_ms * 1e-3) / 1e9) / peak},
             "timing": {"device_ms_per_step": step_ms, "k_scan_ms": scan_ms, "post_ms": ms_post / args.steps, "host_wall_ms_per_step": wall_dev_s * 1e3},
             "clocks": sampler.summary(),
+            "pattern_sweep": sweep,
+            "config1_latency": latency,
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
