@@ -1502,7 +1502,7 @@ size_t resolve_aux_bytes() { return sizeof(EvAux); }
 
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
                            const unsigned long long *uniq, const unsigned long long *n_events_dev, unsigned long long ev_cap, EventOut out,
-                           const ResolveScratch &rs, int num_sms, cudaStream_t s) {
+                           const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side, cudaEvent_t fork_ev, cudaEvent_t join_ev) {
     if (ev_cap == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(rs.ctr, 0, sizeof(ResolveCounters), s);
     if (e != cudaSuccess) return e;
@@ -1517,8 +1517,16 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     }
     k_plan<<<blocks, kPlanWarps * 32, plan_smem, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events_dev, ev_cap, out, items, rs.item_cap,
                                                       rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots);
+    // short and long lines are independent: walk them concurrently when a side stream is given
+    const bool fork = side && fork_ev && join_ev;
+    if (fork) {
+        cudaEventRecord(fork_ev, s);
+        cudaStreamWaitEvent(side, fork_ev, 0);
+    }
+    k_check_long<<<num_sms * 16, 128, 0, fork ? side : s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
+    if (fork) cudaEventRecord(join_ev, side);
     k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
-    k_check_long<<<num_sms * 8, 128, 0, s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
+    if (fork) cudaStreamWaitEvent(s, join_ev, 0);
     unsigned fb = (unsigned)((ev_cap + 127) / 128);
     if (fb > (unsigned)num_sms * 8u) fb = (unsigned)num_sms * 8u;
     k_finalize<<<fb, 128, 0, s>>>(lib.blob, lib.h, uniq, n_events_dev, out, items, rs.results, reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);

@@ -113,7 +113,8 @@ size_t resolve_aux_bytes();
 // n_events is read from device memory (*n_events_dev <= ev_cap, else rs.ctr->overflow is set).
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
                            const unsigned long long *uniq, const unsigned long long *n_events_dev, unsigned long long ev_cap, EventOut out,
-                           const ResolveScratch &rs, int num_sms, cudaStream_t s);
+                           const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side = nullptr, cudaEvent_t fork_ev = nullptr,
+                           cudaEvent_t join_ev = nullptr);
 // Ordering + de-duplication without host involvement for ctr->n_raw <= kSmallSort (otherwise *big_flag = 1 and
 // the caller falls back to launch_sort_unique once it knows the count).
 constexpr int kSmallSort = 16384;

@@ -173,7 +173,8 @@ struct DevWork {
     int any_trailing_cr = 0;
     PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: work that is independent of the main chain
+    cudaEvent_t fork_ev[2] = {nullptr, nullptr}, join_ev[2] = {nullptr, nullptr};
     cudaEvent_t e[10] = {nullptr};   // 0 h2d0, 1 h2d1, 2 scan0, 3 scan1, 4 mid, 5 post0, 6 post1, 7 d2h1, 8 dfa0, 9 dfa1
     uint64_t n_events = 0, n_cand = 0, n_verified = 0;
     bool locked = false, staged = false, scanned = false;
@@ -238,6 +239,11 @@ void release_work(pm_batch *b) {
         for (auto &ev : w.e)
             if (ev) cudaEventDestroy(ev), ev = nullptr;
         if (w.stream) cudaStreamDestroy(w.stream), w.stream = nullptr;
+        if (w.stream2) cudaStreamSynchronize(w.stream2), cudaStreamDestroy(w.stream2), w.stream2 = nullptr;
+        for (int k = 0; k < 2; k++) {
+            if (w.fork_ev[k]) cudaEventDestroy(w.fork_ev[k]), w.fork_ev[k] = nullptr;
+            if (w.join_ev[k]) cudaEventDestroy(w.join_ev[k]), w.join_ev[k] = nullptr;
+        }
         if (w.locked) d->busy.unlock(), w.locked = false;
     }
     b->work.clear();
@@ -319,6 +325,11 @@ int stage(pm_batch *b) {
         w.locked = true;
         CU(cudaSetDevice(d->id));
         CU(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&w.stream2, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; k++) {
+            CU(cudaEventCreateWithFlags(&w.fork_ev[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&w.join_ev[k], cudaEventDisableTiming));
+        }
         for (auto &ev : w.e) CU(cudaEventCreate(&ev));
         const int np = (int)w.pods.size();
         uint64_t off = kHeaderBytes;
@@ -503,7 +514,7 @@ int enqueue_resolve(pm_batch *b, DevWork &w) {
                       w.rs_ctr.as<ResolveCounters>()};
     const unsigned long long *n_unique = reinterpret_cast<const unsigned long long *>(w.ctr.as<char>() + kOffUnique);
     CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), w.uniq.as<unsigned long long>(), n_unique, w.ev_cap,
-                      L.on(w.ev_soa.p), rs, d->num_sms, w.stream));
+                      L.on(w.ev_soa.p), rs, d->num_sms, w.stream, w.stream2, w.fork_ev[1], w.join_ev[1]));
     w.launches += 4;
     CU(cudaEventRecord(w.e[6], w.stream));
     CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
@@ -529,8 +540,13 @@ int scan_async(pm_batch *b) {
         CU(launch_scan(w.text.as<uint8_t>(), w.n_tiles, dl, w.tile_nl.as<uint32_t>(), w.cand.as<unsigned long long>(), w.cand_cap,
                        w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
         CU(cudaEventRecord(w.e[3], w.stream));
-        CU(launch_prefix(w.tile_nl.as<uint32_t>(), w.tile_prefix.as<unsigned long long>(), w.n_tiles, w.scratch.as<unsigned long long>(), w.stream));
-        CU(launch_pods(w.text.as<uint8_t>(), w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), np, w.stream));
+        // the newline prefix and the pod bases only feed the resolve stage: side stream, joined before k_plan
+        CU(cudaEventRecord(w.fork_ev[0], w.stream));
+        CU(cudaStreamWaitEvent(w.stream2, w.fork_ev[0], 0));
+        CU(launch_prefix(w.tile_nl.as<uint32_t>(), w.tile_prefix.as<unsigned long long>(), w.n_tiles, w.scratch.as<unsigned long long>(), w.stream2));
+        CU(launch_pods(w.text.as<uint8_t>(), w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), np, w.stream2));
+        CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream2));
+        CU(cudaEventRecord(w.join_ev[0], w.stream2));
         if ((rc = get(d->pool, w.raw_cap * 8, w.tasks))) return rc;
         if ((rc = get(d->pool, 2 * (size_t)kSmallSort * 8, w.sort_scratch))) return rc;
         CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.tasks.as<unsigned long long>(),
@@ -549,7 +565,7 @@ int scan_async(pm_batch *b) {
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
                              reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream));
         w.launches += 3;
-        CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream));
+        CU(cudaStreamWaitEvent(w.stream, w.join_ev[0], 0));
         CU(cudaEventRecord(w.e[4], w.stream));
         CU(cudaEventRecord(w.e[5], w.stream));
         if ((rc = enqueue_resolve(b, w))) return rc;
