@@ -53,8 +53,10 @@ __device__ __forceinline__ uint32_t not_newline_flags(uint32_t w) {
 }
 
 __device__ __forceinline__ uint32_t newline_mask4(uint32_t w) {   // bit i set iff byte i == '\n'
-    uint32_t x = (~not_newline_flags(w) & 0x80808080u) >> 7;
-    return (x & 1u) | ((x >> 7) & 2u) | ((x >> 14) & 4u) | ((x >> 21) & 8u);
+    // flags at bit 0 of each byte, gathered into bits 21..24 by one multiply (no two partial
+    // products share a bit position, so there are no carries)
+    uint32_t x = (~not_newline_flags(w) >> 7) & 0x01010101u;
+    return ((x * 0x00204081u) >> 21) & 0xFu;
 }
 
 __device__ __forceinline__ uint32_t newline_mask16(const uint4 &v) {
@@ -571,16 +573,18 @@ __global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__r
             for (unsigned long long k = lane; k < len; k += 32) s_line[warp][k] = text[ls + k];
         __syncwarp();
         if (lane == 0) {
-            const uint16_t *tab = tab_fits ? s_tab[warp] : gtab;
-            const uint8_t *cm = s_cmap[warp];
             uint32_t st = 0;
             const uint32_t stride = ud.stride, acc = ud.accept_state, dead = ud.dead_state;
-            if (line_fits) {
-                for (unsigned long long k = 0; k < len && st != acc && st != dead; k++) st = tab[st * stride + cm[s_line[warp][k]]];
+            if (tab_fits && line_fits) {   // everything in shared memory: plain LDS, no generic addressing
+                const uint16_t *tab = s_tab[warp];
+                const uint8_t *cm = s_cmap[warp], *ln = s_line[warp];
+                const uint32_t n32 = (uint32_t)len;
+                for (uint32_t k = 0; k < n32 && st != acc && st != dead; k++) st = tab[st * stride + cm[ln[k]]];
+                if (st != acc) st = tab[st * stride + stride - 1];
             } else {
-                for (unsigned long long k = ls; k < lend && st != acc && st != dead; k++) st = tab[st * stride + cm[text[k]]];
+                for (unsigned long long k = ls; k < lend && st != acc && st != dead; k++) st = gtab[st * stride + gcm[text[k]]];
+                if (st != acc) st = gtab[st * stride + stride - 1];
             }
-            if (st != acc) st = tab[st * stride + stride - 1];
             if (st == acc) {
                 unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
                 if (at < raw_cap)
@@ -1264,7 +1268,11 @@ __global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ 
         const unsigned long long c = (it.len + 31) / 32;
         const unsigned long long ca = min(b, a + lane * c), cb = min(b, ca + c);
         auto walk = [&](uint32_t s, unsigned long long p0, unsigned long long p1) {
-            for (unsigned long long p = p0; p < p1 && s != ut.accept && s != ut.dead; p++) s = ut.tab[s * ut.stride + ut.cmap[text[p]]];
+            if (ut.wide) {
+                for (unsigned long long p = p0; p < p1 && s != ut.accept && s != ut.dead; p++) s = ut.wide[(s << 8) | text[p]];
+            } else {
+                for (unsigned long long p = p0; p < p1 && s != ut.accept && s != ut.dead; p++) s = ut.tab[s * ut.stride + ut.cmap[text[p]]];
+            }
             return s;
         };
         uint32_t in_spec;
