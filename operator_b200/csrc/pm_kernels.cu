@@ -512,12 +512,11 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
 // warp fetches in bulk instead: 512 bytes around the literal in one round trip (newline search by
 // ballot), the pattern's class map and table into shared memory, the line into shared memory;
 // lane 0 then walks the DFA out of shared memory.
-constexpr int kVerifyWarps = 4, kVerifyTable = 4096, kVerifyLine = 512;
+constexpr int kVerifyWarps = 4, kVerifyLine = 512;
 
 __global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h, PodTable pt,
                                                               const unsigned long long *__restrict__ tasks, unsigned long long task_cap,
                                                               unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
-    __shared__ __align__(16) uint16_t s_tab[kVerifyWarps][kVerifyTable / 2];
     __shared__ __align__(16) uint8_t s_cmap[kVerifyWarps][256];
     __shared__ __align__(16) uint8_t s_line[kVerifyWarps][kVerifyLine];
     if (ctr->cand_overflow || ctr->raw_overflow) return;
@@ -563,28 +562,47 @@ __global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__r
         // ---- stage tables and line
         const uint16_t *gtab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off;
         const uint8_t *gcm = blob + h.off_classmaps + ud.classmap_off;
-        const uint32_t n_entries = (uint32_t)ud.nstates * ud.stride;
-        const bool tab_fits = n_entries * 2 <= kVerifyTable, line_fits = len <= kVerifyLine;
+        const bool line_fits = len <= kVerifyLine;
         __syncwarp();
-        if (tab_fits)   // tables start 16-byte aligned in the blob: 128-bit copies (reads up to 14 bytes of the next table's padding)
-            for (uint32_t k = lane; k < (n_entries + 7) / 8; k += 32) reinterpret_cast<uint4 *>(s_tab[warp])[k] = reinterpret_cast<const uint4 *>(gtab)[k];
         for (int k = lane; k < 256 / 4; k += 32) reinterpret_cast<uint32_t *>(s_cmap[warp])[k] = reinterpret_cast<const uint32_t *>(gcm)[k];
         if (line_fits)
             for (unsigned long long k = lane; k < len; k += 32) s_line[warp][k] = text[ls + k];
         __syncwarp();
-        if (lane == 0) {
-            uint32_t st = 0;
-            const uint32_t stride = ud.stride, acc = ud.accept_state, dead = ud.dead_state;
-            if (tab_fits && line_fits) {   // everything in shared memory: plain LDS, no generic addressing
-                const uint16_t *tab = s_tab[warp];
-                const uint8_t *cm = s_cmap[warp], *ln = s_line[warp];
-                const uint32_t n32 = (uint32_t)len;
-                for (uint32_t k = 0; k < n32 && st != acc && st != dead; k++) st = tab[st * stride + cm[ln[k]]];
-                if (st != acc) st = tab[st * stride + stride - 1];
-            } else {
-                for (unsigned long long k = ls; k < lend && st != acc && st != dead; k++) st = gtab[st * stride + gcm[text[k]]];
-                if (st != acc) st = gtab[st * stride + stride - 1];
+        uint32_t st = 0;
+        const uint32_t stride = ud.stride, acc = ud.accept_state, dead = ud.dead_state;
+        if (line_fits) {
+            // Line and class map are in shared memory, the table is read through L1.  All 32 lanes walk: lane i takes bytes [i*c, (i+1)*c) from a
+            // guessed entry state (mid-line idle state warmed up over the 16 bytes in front of its
+            // piece), then the guesses are validated in lane order and a wrong one is redone -- the
+            // speculation of k_check_long, here to cut the serial chain of a ~140-byte line to ~20 steps.
+            const uint16_t *tab = gtab;
+            const uint8_t *cm = s_cmap[warp], *ln = s_line[warp];
+            const uint32_t n32 = (uint32_t)len, c = (n32 + 31) / 32;
+            const uint32_t ca = min(n32, lane * c), cb = min(n32, ca + c);
+            auto walk = [&](uint32_t s0, uint32_t p0, uint32_t p1) {
+                for (uint32_t k = p0; k < p1 && s0 != acc && s0 != dead; k++) s0 = tab[s0 * stride + cm[ln[k]]];
+                return s0;
+            };
+            const uint32_t in_spec = (lane == 0 || ca <= 16) ? walk(0, 0, ca) : walk(ud.mid_state, ca - 16, ca);
+            const uint32_t out_spec = walk(in_spec, ca, cb);
+            uint32_t truth = 0;
+            for (int i = 0; i < 32; i++) {
+                uint32_t in_i = __shfl_sync(FULL, in_spec, i), out_i = __shfl_sync(FULL, out_spec, i);
+                if (in_i != truth) {   // warp-uniform
+                    uint32_t redo = 0;
+                    if (lane == i) redo = walk(truth, ca, cb);
+                    out_i = __shfl_sync(FULL, redo, i);
+                }
+                truth = out_i;
+                if (truth == acc || truth == dead) break;
             }
+            st = truth;
+            if (st != acc) st = tab[st * stride + stride - 1];
+        } else if (lane == 0) {
+            for (unsigned long long k = ls; k < lend && st != acc && st != dead; k++) st = gtab[st * stride + gcm[text[k]]];
+            if (st != acc) st = gtab[st * stride + stride - 1];
+        }
+        if (lane == 0) {
             if (st == acc) {
                 unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
                 if (at < raw_cap)
@@ -956,32 +974,31 @@ __global__ void __launch_bounds__(kSortChunk / 2) k_sort_chunks(const unsigned l
 
 __global__ void __launch_bounds__(256) k_sort_merge(const unsigned long long *__restrict__ chunks, const ScanCounters *ctr, unsigned long long raw_cap,
                                                     unsigned long long *__restrict__ sorted) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned long long *sk = reinterpret_cast<unsigned long long *>(smem_raw);   // all sorted chunks (<= 128 KiB)
     if (sort_too_big(ctr, raw_cap)) return;
     const unsigned long long n = ctr->n_raw;
     const unsigned n_chunks = (unsigned)((n + kSortChunk - 1) / kSortChunk);
+    if (blockIdx.x * blockDim.x >= n_chunks * kSortChunk) return;
+    for (unsigned k = threadIdx.x; k < n_chunks * kSortChunk / 2; k += blockDim.x) reinterpret_cast<uint4 *>(sk)[k] = reinterpret_cast<const uint4 *>(chunks)[k];
+    __syncthreads();
     const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_chunks * kSortChunk) return;
     const unsigned c = i / kSortChunk;
-    const unsigned long long key = chunks[i];
+    const unsigned long long key = sk[i];
     // rank = own index + for every other chunk o the number of its keys that sort before this one
-    // (strictly smaller, or equal with o < c: stable).  The binary searches of all chunks advance in
-    // lock-step so that their loads are independent: ~10 round trips instead of 10 per chunk.
-    unsigned lo[kSortChunks], hi[kSortChunks];
-#pragma unroll
-    for (int o = 0; o < kSortChunks; o++) lo[o] = 0, hi[o] = ((unsigned)o < n_chunks && (unsigned)o != c) ? kSortChunk : 0;
-#pragma unroll 1
-    for (int step = 0; step < 11; step++) {
-#pragma unroll
-        for (int o = 0; o < kSortChunks; o++)
-            if (lo[o] < hi[o]) {
-                unsigned mid = (lo[o] + hi[o]) >> 1;
-                unsigned long long v = chunks[(size_t)o * kSortChunk + mid];
-                if (v < key || (v == key && (unsigned)o < c)) lo[o] = mid + 1; else hi[o] = mid;
-            }
-    }
+    // (strictly smaller, or equal with o < c: stable); binary searches in shared memory
     unsigned rank = i % kSortChunk;
-#pragma unroll
-    for (int o = 0; o < kSortChunks; o++) rank += lo[o];
+    for (unsigned o = 0; o < n_chunks; o++) {
+        if (o == c) continue;
+        const unsigned long long *q = sk + (size_t)o * kSortChunk;
+        unsigned lo = 0, hi = kSortChunk;
+        while (lo < hi) {
+            unsigned mid = (lo + hi) >> 1;
+            unsigned long long v = q[mid];
+            if (v < key || (v == key && o < c)) lo = mid + 1; else hi = mid;
+        }
+        rank += lo;
+    }
     sorted[rank] = key;
 }
 
@@ -996,20 +1013,26 @@ __global__ void __launch_bounds__(1024) k_sort_unique(const unsigned long long *
     }
     const unsigned n = (unsigned)ctr->n_raw;
     constexpr unsigned per = kSmallSort / 1024;
-    // thread t owns keys t, t+1024, ... (coalesced); ranks need a scan per "row": do 16 block scans
-    __shared__ unsigned long long tot;
-    unsigned long long base = 0;
+    // thread t owns the 16 consecutive keys [16t, 16t+16): one block scan of the per-thread counts
+    const unsigned i0 = threadIdx.x * per;
+    unsigned long long k[per];
+    unsigned long long prev = (i0 > 0 && i0 - 1 < n) ? sorted[i0 - 1] : ~0ull;
+    unsigned keep = 0, cnt = 0;
+#pragma unroll
     for (unsigned r = 0; r < per; r++) {
-        unsigned i = r * 1024 + threadIdx.x;
-        if (r * 1024 >= n) break;   // uniform
-        bool keep = i < n && sorted[i] != ~0ull && (i == 0 || sorted[i] != sorted[i - 1]);
-        unsigned long long at = block_exclusive_scan(keep ? 1ull : 0ull, &tot);
-        if (keep) uniq[base + at] = sorted[i];
-        base += tot;
-        __syncthreads();
+        k[r] = (i0 + r < n) ? sorted[i0 + r] : ~0ull;
+        bool kp = k[r] != ~0ull && (i0 + r == 0 || k[r] != prev);
+        prev = k[r];
+        keep |= (unsigned)kp << r;
+        cnt += kp;
     }
+    __shared__ unsigned long long tot;
+    unsigned long long at = block_exclusive_scan(cnt, &tot);
+#pragma unroll
+    for (unsigned r = 0; r < per; r++)
+        if (keep & (1u << r)) uniq[at++] = k[r];
     if (threadIdx.x == 0) {
-        *n_unique = base;
+        *n_unique = tot;
         *big_flag = 0;
     }
 }
@@ -1545,7 +1568,9 @@ cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters 
                               unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s) {
     unsigned long long *chunks = scratch, *sorted = scratch + kSmallSort;
     k_sort_chunks<<<kSortChunks, kSortChunk / 2, 0, s>>>(raw, ctr, raw_cap, chunks);
-    k_sort_merge<<<kSmallSort / 256, 256, 0, s>>>(chunks, ctr, raw_cap, sorted);
+    cudaError_t e = cudaFuncSetAttribute(k_sort_merge, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSort * 8);
+    if (e != cudaSuccess) return e;
+    k_sort_merge<<<kSmallSort / 256, 256, kSmallSort * 8, s>>>(chunks, ctr, raw_cap, sorted);
     k_sort_unique<<<1, 1024, 0, s>>>(sorted, ctr, raw_cap, uniq, n_unique, big_flag);
     return cudaGetLastError();
 }

@@ -167,7 +167,7 @@ struct DevWork {
     uint64_t total = 0, n_tiles = 0;
     uint64_t cand_cap = 0, raw_cap = 0;
     Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, ev_soa, lines_tmp;
-    Buf rs_items, rs_results, rs_long, rs_aux, rs_ctr, h_rs_ctr;   // resolve-stage scratch
+    Buf rs_items, rs_results, rs_long, rs_aux;   // resolve-stage scratch
     Buf tasks, sort_scratch;
     uint64_t item_cap = 0, long_cap = 0, ev_cap = 0;
     int any_trailing_cr = 0;
@@ -179,7 +179,24 @@ struct DevWork {
     uint64_t n_events = 0, n_cand = 0, n_verified = 0;
     bool locked = false, staged = false, scanned = false;
     int launches = 0;
+    // PM_DEBUG_TIMING=1: an event after every stage of the main stream, printed by finish()
+    std::vector<std::pair<const char *, cudaEvent_t>> marks;
+    void mark(const char *name) {
+        static const bool on = getenv("PM_DEBUG_TIMING") != nullptr;
+        if (!on) return;
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        cudaEventRecord(ev, stream);
+        marks.emplace_back(name, ev);
+    }
 };
+
+// Device-side layout of the small counters block `w.ctr`: ScanCounters, then the unique-event
+// count (u64) and the "too many raw events for the one-CTA sort" flag (u32).
+constexpr size_t kOffUnique = sizeof(ScanCounters);
+constexpr size_t kOffBig = sizeof(ScanCounters) + 8;
+constexpr size_t kOffResolve = sizeof(ScanCounters) + 16;   // ResolveCounters live in the same block: one copy back
+constexpr size_t kCtrBytes = sizeof(ScanCounters) + 16 + sizeof(ResolveCounters);
 
 size_t round_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -233,9 +250,9 @@ void release_work(pm_batch *b) {
         Device *d = b->ctx->devs[w.slot];
         cudaSetDevice(d->id);
         if (w.stream) cudaStreamSynchronize(w.stream);
-        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.rs_ctr, &w.tasks, &w.sort_scratch})
+        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.tasks, &w.sort_scratch})
             put(d->pool, *x);
-        for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa, &w.h_rs_ctr}) put(b->ctx->pinned, *x);
+        for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa}) put(b->ctx->pinned, *x);
         for (auto &ev : w.e)
             if (ev) cudaEventDestroy(ev), ev = nullptr;
         if (w.stream) cudaStreamDestroy(w.stream), w.stream = nullptr;
@@ -363,10 +380,10 @@ int stage(pm_batch *b) {
         if ((rc = get(d->pool, (w.n_tiles / 4096 + 2) * 8, w.scratch))) return rc;
         if ((rc = get(d->pool, w.cand_cap * 8, w.cand))) return rc;
         if ((rc = get(d->pool, w.raw_cap * 8, w.raw))) return rc;
-        if ((rc = get(d->pool, sizeof(ScanCounters) + 64, w.ctr))) return rc;
+        if ((rc = get(d->pool, kCtrBytes + 64, w.ctr))) return rc;
         if ((rc = get(d->pool, sizeof(PodDev) * (np + 1), w.pods_dev))) return rc;
-        if ((rc = get(ctx->pinned, sizeof(ScanCounters) + 64, w.h_ctr))) return rc;
-        memset(w.h_ctr.p, 0, sizeof(ScanCounters) + 64);
+        if ((rc = get(ctx->pinned, kCtrBytes + 64, w.h_ctr))) return rc;
+        memset(w.h_ctr.p, 0, kCtrBytes + 64);
         CU(cudaMemcpyAsync(w.pods_dev.p, hp, sizeof(PodDev) * np, cudaMemcpyHostToDevice, w.stream));
         CU(cudaEventRecord(w.e[0], w.stream));
         for (int k = 0; k < np; k++) {
@@ -477,18 +494,11 @@ int maybe_adapt(pm_library *l, DevWork &w) {
     return PM_OK;
 }
 
-// Device-side layout of the small counters block `w.ctr`: ScanCounters, then the unique-event
-// count (u64) and the "too many raw events for the one-CTA sort" flag (u32).
-constexpr size_t kOffUnique = sizeof(ScanCounters);
-constexpr size_t kOffBig = sizeof(ScanCounters) + 8;
-constexpr size_t kCtrBytes = sizeof(ScanCounters) + 16;
-
 // Scratch of the resolve stage for up to ev_cap events (grow-only).
 int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
     pm_ctx *ctx = b->ctx;
     Device *d = ctx->devs[w.slot];
-    if (ev_cap < w.ev_cap) ev_cap = w.ev_cap;
-    w.ev_cap = ev_cap;
+    w.ev_cap = ev_cap;   // the result arrays are copied back at this capacity: keep it near the event count
     w.item_cap = std::min<uint64_t>(std::max<uint64_t>(w.item_cap, tiny_queues() ? 16 : ev_cap * 96 + (1u << 16)), 0xFFFFFFF0ull);
     w.long_cap = std::max<uint64_t>(w.long_cap, w.item_cap / 8 + (1u << 12));
     SoaLayout L(ev_cap);
@@ -499,8 +509,6 @@ int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
     if ((rc = get(d->pool, w.item_cap, w.rs_results))) return rc;
     if ((rc = get(d->pool, w.long_cap * 4, w.rs_long))) return rc;
     if ((rc = get(d->pool, ev_cap * resolve_aux_bytes(), w.rs_aux))) return rc;
-    if ((rc = get(d->pool, sizeof(ResolveCounters), w.rs_ctr))) return rc;
-    if ((rc = get(ctx->pinned, sizeof(ResolveCounters), w.h_rs_ctr))) return rc;
     if ((rc = get(d->pool, ev_cap * 8 + 64, w.uniq))) return rc;
     return PM_OK;
 }
@@ -511,16 +519,17 @@ int enqueue_resolve(pm_batch *b, DevWork &w) {
     const DeviceLibrary &dl = b->lib->dev[w.slot];
     SoaLayout L(w.ev_cap);
     ResolveScratch rs{w.rs_items.p, w.item_cap, w.rs_results.as<unsigned char>(), w.rs_long.as<uint32_t>(), w.long_cap, w.rs_aux.p,
-                      w.rs_ctr.as<ResolveCounters>()};
+                      reinterpret_cast<ResolveCounters *>(w.ctr.as<char>() + kOffResolve)};
     const unsigned long long *n_unique = reinterpret_cast<const unsigned long long *>(w.ctr.as<char>() + kOffUnique);
     CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), w.uniq.as<unsigned long long>(), n_unique, w.ev_cap,
                       L.on(w.ev_soa.p), rs, d->num_sms, w.stream, w.stream2, w.fork_ev[1], w.join_ev[1]));
     w.launches += 4;
+    w.mark("resolve (plan,check,finalize)");
     CU(cudaEventRecord(w.e[6], w.stream));
     CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
-    CU(cudaMemcpyAsync(w.h_rs_ctr.p, w.rs_ctr.p, sizeof(ResolveCounters), cudaMemcpyDeviceToHost, w.stream));
     CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, kCtrBytes, cudaMemcpyDeviceToHost, w.stream));
     CU(cudaEventRecord(w.e[7], w.stream));
+    w.mark("result copies");
     return PM_OK;
 }
 
@@ -533,13 +542,19 @@ int scan_async(pm_batch *b) {
         CU(cudaSetDevice(d->id));
         const DeviceLibrary &dl = b->lib->dev[w.slot];
         const int np = (int)w.pods.size();
-        int rc = ensure_resolve_scratch(b, w, kSmallSort);
+        // capacity of the result arrays: everything the small sort can deliver on the first scan of a
+        // batch, the last event count plus 12 % on a re-scan (less to copy back)
+        uint64_t want = kSmallSort;
+        if (w.scanned) want = std::min<uint64_t>(kSmallSort, round_up(w.n_events + w.n_events / 8 + 64, 256));
+        int rc = ensure_resolve_scratch(b, w, want);
         if (rc) return rc;
         CU(cudaMemsetAsync(w.ctr.p, 0, kCtrBytes, w.stream));
+        w.mark("start");
         CU(cudaEventRecord(w.e[2], w.stream));
         CU(launch_scan(w.text.as<uint8_t>(), w.n_tiles, dl, w.tile_nl.as<uint32_t>(), w.cand.as<unsigned long long>(), w.cand_cap,
                        w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
         CU(cudaEventRecord(w.e[3], w.stream));
+        w.mark("k_scan");
         // the newline prefix and the pod bases only feed the resolve stage: side stream, joined before k_plan
         CU(cudaEventRecord(w.fork_ev[0], w.stream));
         CU(cudaStreamWaitEvent(w.stream2, w.fork_ev[0], 0));
@@ -552,6 +567,7 @@ int scan_async(pm_batch *b) {
         CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.tasks.as<unsigned long long>(),
                           w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), d->num_sms, w.stream));
         w.launches += 1 + 3 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
+        w.mark("confirm+verify");
         CU(cudaEventRecord(w.e[8], w.stream));
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
             const GroupDesc &gd = reinterpret_cast<const GroupDesc *>(b->lib->lib.blob.data() + dl.h.off_groups)[g];
@@ -565,7 +581,9 @@ int scan_async(pm_batch *b) {
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
                              reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream));
         w.launches += 3;
+        w.mark("sort");
         CU(cudaStreamWaitEvent(w.stream, w.join_ev[0], 0));
+        w.mark("join prefix/pods");
         CU(cudaEventRecord(w.e[4], w.stream));
         CU(cudaEventRecord(w.e[5], w.stream));
         if ((rc = enqueue_resolve(b, w))) return rc;
@@ -625,11 +643,18 @@ int finish(pm_batch *b, pm_result_view *out) {
             if ((rc = enqueue_resolve(b, w))) return rc;
             CU(cudaStreamSynchronize(w.stream));
         }
-        while (w.h_rs_ctr.as<ResolveCounters>()->overflow) {
-            w.item_cap = std::min<uint64_t>(w.item_cap * 4, 0xFFFFFFF0ull);
-            w.long_cap *= 4;
+        while (reinterpret_cast<ResolveCounters *>(w.h_ctr.as<char>() + kOffResolve)->overflow) {
+            const uint64_t n_unique = *reinterpret_cast<unsigned long long *>(w.h_ctr.as<char>() + kOffUnique);
             int rc;
-            if ((rc = ensure_resolve_scratch(b, w, w.ev_cap))) return rc;
+            if (n_unique > w.ev_cap) {   // more events than the result arrays were sized for
+                uint64_t cap = w.ev_cap;
+                while (cap < n_unique) cap <<= 1;
+                if ((rc = ensure_resolve_scratch(b, w, cap))) return rc;
+            } else {
+                w.item_cap = std::min<uint64_t>(w.item_cap * 4, 0xFFFFFFF0ull);
+                w.long_cap *= 4;
+                if ((rc = ensure_resolve_scratch(b, w, w.ev_cap))) return rc;
+            }
             if ((rc = enqueue_resolve(b, w))) return rc;
             CU(cudaStreamSynchronize(w.stream));
         }
@@ -664,6 +689,15 @@ int finish(pm_batch *b, pm_result_view *out) {
         ms_post = std::max<double>(ms_post, p1 + p2);
         ms_d2h = std::max<double>(ms_d2h, dd);
         w.scanned = true;
+        if (!w.marks.empty()) {
+            for (size_t k = 1; k < w.marks.size(); k++) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, w.marks[k - 1].second, w.marks[k].second);
+                fprintf(stderr, "[pm timing] %-32s %8.1f us\n", w.marks[k].first, ms * 1e3);
+            }
+            for (auto &mk : w.marks) cudaEventDestroy(mk.second);
+            w.marks.clear();
+        }
         int rs = maybe_adapt(b->lib, w);
         if (rs) return rs;
     }
