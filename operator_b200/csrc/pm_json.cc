@@ -203,6 +203,126 @@ bool json_parse(const char *data, size_t n, JsonValue &out, std::string &err, si
     return ok;
 }
 
+bool json_find_top_level_string(const char *s, size_t n, const char *key, size_t *begin, size_t *end) {
+    const size_t klen = strlen(key);
+    int depth = 0;
+    size_t i = 0;
+    bool expect_key = false;
+    while (i < n) {
+        char c = s[i];
+        if (c == '"') {
+            size_t j = i + 1;
+            while (j < n && s[j] != '"') j += (s[j] == '\\' && j + 1 < n) ? 2 : 1;
+            if (j >= n) return false;
+            if (depth == 1 && expect_key) {
+                bool is_key = (j - i - 1 == klen) && !memcmp(s + i + 1, key, klen);
+                size_t k = j + 1;
+                while (k < n && (s[k] == ' ' || s[k] == '\t' || s[k] == '\n' || s[k] == '\r')) k++;
+                if (k < n && s[k] == ':') {
+                    k++;
+                    while (k < n && (s[k] == ' ' || s[k] == '\t' || s[k] == '\n' || s[k] == '\r')) k++;
+                    if (is_key) {
+                        if (k >= n || s[k] != '"') return false;
+                        size_t e = k + 1;
+                        while (e < n && s[e] != '"') e += (s[e] == '\\' && e + 1 < n) ? 2 : 1;
+                        if (e >= n) return false;
+                        *begin = k + 1;
+                        *end = e;
+                        return true;
+                    }
+                    expect_key = false;
+                    i = k;
+                    continue;
+                }
+            }
+            i = j + 1;
+            continue;
+        }
+        if (c == '{' || c == '[') {
+            depth++;
+            expect_key = (c == '{' && depth == 1);
+        } else if (c == '}' || c == ']') {
+            depth--;
+        } else if (c == ',' && depth == 1) {
+            expect_key = true;
+        }
+        i++;
+    }
+    return false;
+}
+
+size_t json_decode_string(const char *data, size_t n, char *out) {
+    std::string tmp;
+    std::string quoted;
+    // reuse the parser's string routine on a quoted copy only when escapes are present; the common
+    // log has few escapes per kilobyte, so copy runs between backslashes directly
+    size_t o = 0, i = 0;
+    while (i < n) {
+        const char *q = (const char *)memchr(data + i, '\\', n - i);
+        size_t run = q ? (size_t)(q - (data + i)) : n - i;
+        memcpy(out + o, data + i, run);
+        o += run;
+        i += run;
+        if (i >= n) break;
+        if (i + 1 >= n) return (size_t)-1;
+        char c = data[i + 1];
+        i += 2;
+        switch (c) {
+            case '"': out[o++] = '"'; break;
+            case '\\': out[o++] = '\\'; break;
+            case '/': out[o++] = '/'; break;
+            case 'b': out[o++] = '\b'; break;
+            case 'f': out[o++] = '\f'; break;
+            case 'n': out[o++] = '\n'; break;
+            case 'r': out[o++] = '\r'; break;
+            case 't': out[o++] = '\t'; break;
+            case 'u': {
+                auto hex4 = [&](size_t at, uint32_t &v) {
+                    if (at + 4 > n) return false;
+                    v = 0;
+                    for (int k = 0; k < 4; k++) {
+                        char h = data[at + k];
+                        int d = (h >= '0' && h <= '9') ? h - '0' : (h >= 'a' && h <= 'f') ? h - 'a' + 10 : (h >= 'A' && h <= 'F') ? h - 'A' + 10 : -1;
+                        if (d < 0) return false;
+                        v = v * 16 + d;
+                    }
+                    return true;
+                };
+                uint32_t v;
+                if (!hex4(i, v)) return (size_t)-1;
+                i += 4;
+                if (v >= 0xD800 && v <= 0xDBFF && i + 6 <= n && data[i] == '\\' && data[i + 1] == 'u') {
+                    uint32_t lo;
+                    if (hex4(i + 2, lo) && lo >= 0xDC00 && lo <= 0xDFFF) {
+                        v = 0x10000 + ((v - 0xD800) << 10) + (lo - 0xDC00);
+                        i += 6;
+                    }
+                }
+                if (v >= 0xD800 && v <= 0xDFFF) v = 0xFFFD;
+                tmp.clear();
+                if (v < 0x80) {
+                    out[o++] = (char)v;
+                } else if (v < 0x800) {
+                    out[o++] = (char)(0xC0 | (v >> 6));
+                    out[o++] = (char)(0x80 | (v & 0x3F));
+                } else if (v < 0x10000) {
+                    out[o++] = (char)(0xE0 | (v >> 12));
+                    out[o++] = (char)(0x80 | ((v >> 6) & 0x3F));
+                    out[o++] = (char)(0x80 | (v & 0x3F));
+                } else {
+                    out[o++] = (char)(0xF0 | (v >> 18));
+                    out[o++] = (char)(0x80 | ((v >> 12) & 0x3F));
+                    out[o++] = (char)(0x80 | ((v >> 6) & 0x3F));
+                    out[o++] = (char)(0x80 | (v & 0x3F));
+                }
+                break;
+            }
+            default: return (size_t)-1;
+        }
+    }
+    return o;
+}
+
 void json_escape(const std::string &s, std::string &out) {
     out.push_back('"');
     for (unsigned char c : s) {

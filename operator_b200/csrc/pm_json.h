@@ -28,6 +28,13 @@ struct JsonValue {
 // Returns false and fills err (with byte offset) on malformed input.
 bool json_parse(const char *data, size_t n, JsonValue &out, std::string &err, size_t *err_off = nullptr);
 
+// Span of the string VALUE of a top-level key (the bytes between its quotes, still escaped).
+// Lets a large member (the pod log) be taken out of a request without building a DOM for it.
+bool json_find_top_level_string(const char *data, size_t n, const char *key, size_t *begin, size_t *end);
+// Decodes the escaped string body [data, data+n) to UTF-8 at `out` (capacity >= n); returns the
+// decoded length or (size_t)-1 on a malformed escape.
+size_t json_decode_string(const char *data, size_t n, char *out);
+
 void json_escape(const std::string &s, std::string &out);   // appends a quoted JSON string
 std::string json_number(double v);                          // shortest round-trip repr
 

@@ -126,6 +126,7 @@ struct pm_library {
     std::vector<void *> dev_blobs;
     std::vector<AdaptState> adapt;
     pm_ctx *owner = nullptr;
+    uint64_t generation = 0;   // unique per compiled library (result-cache key of pm_parse)
 };
 
 struct pm_ctx {
@@ -860,8 +861,10 @@ int pm_library_compile(pm_ctx *ctx, const uint8_t *spec, size_t n, pm_library **
     if (!rep) rep = &local;
     if (!out || !spec) return fail(PM_E_INVALID, "null argument");
     *out = nullptr;
+    static std::atomic<uint64_t> next_generation{1};
     pm_library *l = new pm_library();
     l->owner = ctx;
+    l->generation = next_generation.fetch_add(1);
     int rc = compile_library(reinterpret_cast<const char *>(spec), n, l->lib, *rep);
     if (rc != PM_OK) {
         delete l;
@@ -1056,4 +1059,11 @@ pm_library *ctx_current_library(pm_ctx *ctx) {
     return ctx->current;
 }
 const CompiledLibrary &library_compiled(const pm_library *l) { return l->lib; }
+uint64_t library_generation(const pm_library *l) { return l->generation; }
+void *ctx_pinned_get(pm_ctx *ctx, size_t bytes, size_t *cap) {
+    void *p = nullptr;
+    if (ctx->pinned.get(bytes, &p, cap) != PM_OK) return nullptr;
+    return p;
+}
+void ctx_pinned_put(pm_ctx *ctx, void *p, size_t cap) { ctx->pinned.put(p, cap); }
 }  // namespace pm

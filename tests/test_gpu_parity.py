@@ -239,6 +239,22 @@ def test_parse_contract(engine):
     assert out["metadata"]["podName"] == "orders-7d9f"
     empty = LogParserClient(engine).analyze_log({"pod": {"metadata": {"name": "p"}}, "logs": "", "events": []})
     assert empty["events"] == [] and empty["summary"]["highestSeverity"] == "NONE"
+    # escapes in the log (json.dumps emits \\uXXXX and surrogate pairs for non-ASCII), decoded straight into pinned memory
+    uni = "caf\u00e9 \u20ac100 \U0001F600 \"quoted\" back\\slash\n" + wit[3] + " \u00e9\n" + chr(9) + "at x.Y(Z.java:1)\n"
+    out_u = LogParserClient(engine).analyze_log({"pod": {"metadata": {"name": "u"}}, "logs": uni, "events": []})
+    ev_u = oracle.analyze(uni.encode("utf-8"), olib)
+    assert [o["lineNumber"] for o in out_u["events"]] == [e.line_no for e in ev_u] and len(ev_u) >= 1
+    assert out_u["events"][0]["context"]["matchedLine"] == uni.split("\n")[1]
+    # result cache: the operator re-posts the same failure (one request per matching CR, every reconcile)
+    req2 = {"pod": {"metadata": {"name": "orders-7d9f", "namespace": "shop", "uid": "uid-123"},
+                    "status": {"containerStatuses": [{"state": {"terminated": {"exitCode": 1, "finishedAt": "2026-03-03T09:27:00Z"}}}]}},
+            "logs": text, "events": []}
+    first = LogParserClient(engine).analyze_log(req2)
+    again = LogParserClient(engine).analyze_log(req2)
+    assert again == first and again["analysisId"] == first["analysisId"]       # served from the cache
+    req2["pod"]["status"]["containerStatuses"][0]["state"]["terminated"]["finishedAt"] = "2026-03-03T09:30:00Z"
+    later = LogParserClient(engine).analyze_log(req2)
+    assert later["analysisId"] != first["analysisId"] and later["events"] == first["events"]
 
 
 def test_golden_fixtures(engine):
