@@ -15,6 +15,9 @@
  *   - buffers that cross the ABI are owned by the C side (pm_host_alloc / result views);
  *     the caller never frees anything but through the matching pm_* call;
  *   - pm_ctx and a published pm_library are thread-safe; a pm_batch belongs to one thread;
+ *   - a device runs one batch at a time: pm_batch_stage/submit block while another batch holds the
+ *     device and until that batch is released (so release a batch before the same thread stages
+ *     the next one on the same devices);
  *   - there is no CPU fallback: without a usable CUDA device pm_init fails.
  */
 #ifndef PODMORTEM_SCAN_H
