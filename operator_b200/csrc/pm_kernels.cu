@@ -1056,9 +1056,11 @@ struct Item {
     uint32_t unit;
 };
 
-struct EvAux {
+struct EvAux {                           // what k_plan learns about one key, indexed like keys[] (64 bytes)
     unsigned long long item_base;
     int32_t n_stack, na;
+    int32_t pod, line_no, line_len, ctx_first, ctx_last, pad;
+    int64_t line_start, ctx_start, ctx_end;
 };
 
 // Collects positions of the next `need` '\n' bytes at positions >= from into out[0..need).
@@ -1133,8 +1135,8 @@ __device__ void warp_collect_backward(const uint8_t *text, unsigned long long be
 
 __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
                                                           const unsigned long long *__restrict__ tile_prefix, PodTable pt,
-                                                          const unsigned long long *__restrict__ uniq, const unsigned long long *n_events_ptr,
-                                                          unsigned long long ev_cap, EventOut out,
+                                                          const unsigned long long *__restrict__ keys, const unsigned long long *n_keys_ptr,
+                                                          unsigned long long key_cap,
                                                           Item *__restrict__ items, unsigned long long item_cap, uint32_t *__restrict__ long_list,
                                                           unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr, int slots) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1144,14 +1146,17 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
     const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
     const PodDev *pods = pt.pods;
-    const unsigned long long n_events = *n_events_ptr;
-    if (n_events > ev_cap) {
+    // keys[] may be the raw (unsorted, possibly duplicated) event queue: a duplicate plans the
+    // same work twice and k_finalize writes the same row twice.  More keys than key_cap means
+    // the caller will come back through the sorted path: nothing to do here.
+    const unsigned long long n_events = *n_keys_ptr;
+    if (n_events > key_cap) {
         if (threadIdx.x == 0 && blockIdx.x == 0) ctr->overflow = 1;
         return;
     }
 
     for (unsigned long long ev = (unsigned long long)blockIdx.x * kPlanWarps + warp; ev < n_events; ev += (unsigned long long)gridDim.x * kPlanWarps) {
-        const unsigned long long key = uniq[ev], ls = key >> kPatternBits;
+        const unsigned long long key = keys[ev], ls = key >> kPatternBits;
         const uint32_t pat = (uint32_t)(key & ((1u << kPatternBits) - 1u));
         const PatternDesc pd = pds[pat];
         int lo = 0, hi = pt.n - 1;   // pod = last pod with start <= ls
@@ -1238,16 +1243,19 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
             line_span(0, la, lb);
             line_span(-nb, ca, cb);
             line_span(na, ea, eb);
-            out.pod[ev] = lo;
-            out.pattern[ev] = (int32_t)pat;
-            out.line_no[ev] = (int32_t)L;
-            out.line_start[ev] = (int64_t)(ls - pod.start);
-            out.line_len[ev] = (int32_t)(lb - la);
-            out.ctx_first[ev] = (int32_t)(L - nb);
-            out.ctx_last[ev] = (int32_t)(L + na);            // k_finalize adds the STACK run
-            out.ctx_start[ev] = (int64_t)(ca - pod.start);
-            out.ctx_end[ev] = (int64_t)(eb - pod.start);
-            EvAux ax{base, n_stack, na};
+            EvAux ax;
+            ax.item_base = base;
+            ax.n_stack = n_stack;
+            ax.na = na;
+            ax.pod = lo;
+            ax.line_no = (int32_t)L;
+            ax.line_len = (int32_t)(lb - la);
+            ax.ctx_first = (int32_t)(L - nb);
+            ax.ctx_last = (int32_t)(L + na);                 // k_finalize adds the STACK run
+            ax.pad = 0;
+            ax.line_start = (int64_t)(ls - pod.start);
+            ax.ctx_start = (int64_t)(ca - pod.start);
+            ax.ctx_end = (int64_t)(eb - pod.start);
             aux[ev] = ax;
         }
         __syncwarp();
@@ -1321,25 +1329,41 @@ __global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ 
     }
 }
 
-__global__ void __launch_bounds__(128) k_finalize(const uint8_t *__restrict__ blob, BlobHeader h, const unsigned long long *__restrict__ uniq,
-                                                  const unsigned long long *n_events_ptr, EventOut out, const Item *__restrict__ items,
-                                                  const unsigned char *__restrict__ results, const EvAux *__restrict__ aux, const PodTable pt,
-                                                  const ResolveCounters *ctr) {
+// One thread per key.  The row of a key goes to out[rank], rank = position of the key in the
+// sorted, de-duplicated uniq[]; so keys[] can be the raw queue, planned and checked while the sort
+// was still running on another stream (duplicates write identical rows).
+__global__ void __launch_bounds__(128) k_finalize(const uint8_t *__restrict__ blob, BlobHeader h, const unsigned long long *__restrict__ keys,
+                                                  const unsigned long long *n_keys_ptr, const unsigned long long *__restrict__ uniq,
+                                                  const unsigned long long *n_unique_ptr, unsigned long long ev_cap, EventOut out,
+                                                  const Item *__restrict__ items, const unsigned char *__restrict__ results,
+                                                  const EvAux *__restrict__ aux, const PodTable pt, ResolveCounters *ctr) {
     if (ctr->overflow) return;
-    const unsigned long long n_events = *n_events_ptr;
+    const unsigned long long n_keys = *n_keys_ptr, n_unique = *n_unique_ptr;
+    if (n_unique > ev_cap) {
+        if (threadIdx.x == 0 && blockIdx.x == 0) ctr->overflow = 1;
+        return;
+    }
     const PatternDesc *pds = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
-    for (unsigned long long ev = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; ev < n_events; ev += (unsigned long long)gridDim.x * blockDim.x) {
-        const uint32_t pat = (uint32_t)(uniq[ev] & ((1u << kPatternBits) - 1u));
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_keys; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long key = keys[i];
+        unsigned long long lo = 0, hi = n_unique;            // lower bound; the key is present
+        while (lo < hi) {
+            unsigned long long mid = (lo + hi) >> 1;
+            if (uniq[mid] < key) lo = mid + 1; else hi = mid;
+        }
+        const unsigned long long ev = lo;
+        if (ev >= n_unique || uniq[ev] != key) continue;
+        const uint32_t pat = (uint32_t)(key & ((1u << kPatternBits) - 1u));
         const PatternDesc pd = pds[pat];
-        const EvAux ax = aux[ev];
+        const EvAux ax = aux[i];
         // context: leading run of STACK lines after the lines_after window
         int run = 0;
         while (run < ax.n_stack && results[ax.item_base + run]) run++;
+        int64_t ctx_end = ax.ctx_end;
         if (run > 0) {
             const Item it = items[ax.item_base + run - 1];
-            out.ctx_last[ev] += run;
-            out.ctx_end[ev] = (int64_t)(it.a + it.len - pt.pods[out.pod[ev]].start);
+            ctx_end = (int64_t)(it.a + it.len - pt.pods[ax.pod].start);
         }
         // score: secondaries in order, nearest matching line (SPEC.md section 5)
         double acc = 0.0;
@@ -1359,6 +1383,15 @@ __global__ void __launch_bounds__(128) k_finalize(const uint8_t *__restrict__ bl
             }
             off += cnt;
         }
+        out.pod[ev] = ax.pod;
+        out.pattern[ev] = (int32_t)pat;
+        out.line_no[ev] = ax.line_no;
+        out.line_start[ev] = ax.line_start;
+        out.line_len[ev] = ax.line_len;
+        out.ctx_first[ev] = ax.ctx_first;
+        out.ctx_last[ev] = ax.ctx_last + run;
+        out.ctx_start[ev] = ax.ctx_start;
+        out.ctx_end[ev] = ctx_end;
         out.score[ev] = __dmul_rn(__dmul_rn(pd.confidence, pd.mult), __dadd_rn(1.0, acc));
     }
 }
@@ -1532,12 +1565,14 @@ size_t resolve_item_bytes() { return sizeof(Item); }
 size_t resolve_aux_bytes() { return sizeof(EvAux); }
 
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
-                           const unsigned long long *uniq, const unsigned long long *n_events_dev, unsigned long long ev_cap, EventOut out,
-                           const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side, cudaEvent_t fork_ev, cudaEvent_t join_ev) {
-    if (ev_cap == 0) return cudaSuccess;
+                           const unsigned long long *keys, const unsigned long long *n_keys_dev, unsigned long long key_cap,
+                           const unsigned long long *uniq, const unsigned long long *n_unique_dev, unsigned long long ev_cap, EventOut out,
+                           const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side, cudaEvent_t fork_ev, cudaEvent_t join_ev,
+                           cudaEvent_t uniq_ready) {
+    if (ev_cap == 0 || key_cap == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(rs.ctr, 0, sizeof(ResolveCounters), s);
     if (e != cudaSuccess) return e;
-    unsigned blocks = (unsigned)((ev_cap + kPlanWarps - 1) / kPlanWarps);
+    unsigned blocks = (unsigned)((key_cap + kPlanWarps - 1) / kPlanWarps);
     if (blocks > (unsigned)num_sms * 16u) blocks = (unsigned)num_sms * 16u;
     Item *items = reinterpret_cast<Item *>(rs.items);
     int slots = lib.ctx_slots > 0 ? lib.ctx_slots : kCtxSlots;
@@ -1546,7 +1581,7 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
         e = cudaFuncSetAttribute(k_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem);
         if (e != cudaSuccess) return e;
     }
-    k_plan<<<blocks, kPlanWarps * 32, plan_smem, s>>>(text, lib.blob, lib.h, tile_prefix, pt, uniq, n_events_dev, ev_cap, out, items, rs.item_cap,
+    k_plan<<<blocks, kPlanWarps * 32, plan_smem, s>>>(text, lib.blob, lib.h, tile_prefix, pt, keys, n_keys_dev, key_cap, items, rs.item_cap,
                                                       rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots);
     // short and long lines are independent: walk them concurrently when a side stream is given
     const bool fork = side && fork_ev && join_ev;
@@ -1558,9 +1593,11 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     if (fork) cudaEventRecord(join_ev, side);
     k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
     if (fork) cudaStreamWaitEvent(s, join_ev, 0);
-    unsigned fb = (unsigned)((ev_cap + 127) / 128);
+    if (uniq_ready) cudaStreamWaitEvent(s, uniq_ready, 0);   // the sort ran beside plan/check
+    unsigned fb = (unsigned)((key_cap + 127) / 128);
     if (fb > (unsigned)num_sms * 8u) fb = (unsigned)num_sms * 8u;
-    k_finalize<<<fb, 128, 0, s>>>(lib.blob, lib.h, uniq, n_events_dev, out, items, rs.results, reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);
+    k_finalize<<<fb, 128, 0, s>>>(lib.blob, lib.h, keys, n_keys_dev, uniq, n_unique_dev, ev_cap, out, items, rs.results,
+                                  reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);
     return cudaGetLastError();
 }
 

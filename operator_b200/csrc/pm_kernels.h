@@ -110,11 +110,16 @@ size_t resolve_item_bytes();
 size_t resolve_aux_bytes();
 // Four launches (k_plan, k_check, k_check_long, k_finalize).  If rs.ctr->overflow is set afterwards the
 // scratch was too small and the outputs are incomplete: call again with larger capacities.
-// n_events is read from device memory (*n_events_dev <= ev_cap, else rs.ctr->overflow is set).
+// keys[0, *n_keys_dev) is what gets planned and checked (rs.aux holds key_cap entries): either uniq itself,
+// or the raw event queue while the sort that produces uniq is still running on another stream -
+// then uniq_ready is the event recorded after that sort, waited for just before k_finalize, which
+// places each key's row at its rank in uniq[0, *n_unique_dev).  All counts are read on the device;
+// *n_keys_dev > key_cap or *n_unique_dev > ev_cap sets rs.ctr->overflow.
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
-                           const unsigned long long *uniq, const unsigned long long *n_events_dev, unsigned long long ev_cap, EventOut out,
+                           const unsigned long long *keys, const unsigned long long *n_keys_dev, unsigned long long key_cap,
+                           const unsigned long long *uniq, const unsigned long long *n_unique_dev, unsigned long long ev_cap, EventOut out,
                            const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side = nullptr, cudaEvent_t fork_ev = nullptr,
-                           cudaEvent_t join_ev = nullptr);
+                           cudaEvent_t join_ev = nullptr, cudaEvent_t uniq_ready = nullptr);
 // Ordering + de-duplication without host involvement for ctr->n_raw <= kSmallSort (otherwise *big_flag = 1 and
 // the caller falls back to launch_sort_unique once it knows the count).
 constexpr int kSmallSort = 16384;

@@ -174,8 +174,9 @@ struct DevWork {
     int any_trailing_cr = 0;
     PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
-    cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: work that is independent of the main chain
-    cudaEvent_t fork_ev[2] = {nullptr, nullptr}, join_ev[2] = {nullptr, nullptr};
+    cudaStream_t stream = nullptr, stream2 = nullptr, stream3 = nullptr;   // 2, 3: work that is independent of the main chain
+    cudaEvent_t fork_ev[3] = {nullptr, nullptr, nullptr}, join_ev[3] = {nullptr, nullptr, nullptr};
+    uint64_t key_cap = 0;   // entries of rs_aux (keys the resolve stage can plan in one go)
     cudaEvent_t e[10] = {nullptr};   // 0 h2d0, 1 h2d1, 2 scan0, 3 scan1, 4 mid, 5 post0, 6 post1, 7 d2h1, 8 dfa0, 9 dfa1
     uint64_t n_events = 0, n_cand = 0, n_verified = 0;
     bool locked = false, staged = false, scanned = false;
@@ -258,7 +259,8 @@ void release_work(pm_batch *b) {
             if (ev) cudaEventDestroy(ev), ev = nullptr;
         if (w.stream) cudaStreamDestroy(w.stream), w.stream = nullptr;
         if (w.stream2) cudaStreamSynchronize(w.stream2), cudaStreamDestroy(w.stream2), w.stream2 = nullptr;
-        for (int k = 0; k < 2; k++) {
+        if (w.stream3) cudaStreamSynchronize(w.stream3), cudaStreamDestroy(w.stream3), w.stream3 = nullptr;
+        for (int k = 0; k < 3; k++) {
             if (w.fork_ev[k]) cudaEventDestroy(w.fork_ev[k]), w.fork_ev[k] = nullptr;
             if (w.join_ev[k]) cudaEventDestroy(w.join_ev[k]), w.join_ev[k] = nullptr;
         }
@@ -344,7 +346,8 @@ int stage(pm_batch *b) {
         CU(cudaSetDevice(d->id));
         CU(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&w.stream2, cudaStreamNonBlocking));
-        for (int k = 0; k < 2; k++) {
+        CU(cudaStreamCreateWithFlags(&w.stream3, cudaStreamNonBlocking));
+        for (int k = 0; k < 3; k++) {
             CU(cudaEventCreateWithFlags(&w.fork_ev[k], cudaEventDisableTiming));
             CU(cudaEventCreateWithFlags(&w.join_ev[k], cudaEventDisableTiming));
         }
@@ -509,21 +512,28 @@ int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
     if ((rc = get(d->pool, w.item_cap * resolve_item_bytes(), w.rs_items))) return rc;
     if ((rc = get(d->pool, w.item_cap, w.rs_results))) return rc;
     if ((rc = get(d->pool, w.long_cap * 4, w.rs_long))) return rc;
-    if ((rc = get(d->pool, ev_cap * resolve_aux_bytes(), w.rs_aux))) return rc;
+    // the resolve stage plans either the sorted events (<= ev_cap) or the raw queue (<= kSmallSort)
+    w.key_cap = std::max<uint64_t>(ev_cap, std::min<uint64_t>(w.raw_cap, kSmallSort));
+    if ((rc = get(d->pool, w.key_cap * resolve_aux_bytes(), w.rs_aux))) return rc;
     if ((rc = get(d->pool, ev_cap * 8 + 64, w.uniq))) return rc;
     return PM_OK;
 }
 
 // Enqueues the resolve stage and the result copies; the event count is read on the device.
-int enqueue_resolve(pm_batch *b, DevWork &w) {
+// from_raw: plan and check the raw queue while the sort is still running on stream3 (join_ev[2]).
+int enqueue_resolve(pm_batch *b, DevWork &w, bool from_raw = false) {
     Device *d = b->ctx->devs[w.slot];
     const DeviceLibrary &dl = b->lib->dev[w.slot];
     SoaLayout L(w.ev_cap);
     ResolveScratch rs{w.rs_items.p, w.item_cap, w.rs_results.as<unsigned char>(), w.rs_long.as<uint32_t>(), w.long_cap, w.rs_aux.p,
                       reinterpret_cast<ResolveCounters *>(w.ctr.as<char>() + kOffResolve)};
     const unsigned long long *n_unique = reinterpret_cast<const unsigned long long *>(w.ctr.as<char>() + kOffUnique);
-    CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), w.uniq.as<unsigned long long>(), n_unique, w.ev_cap,
-                      L.on(w.ev_soa.p), rs, d->num_sms, w.stream, w.stream2, w.fork_ev[1], w.join_ev[1]));
+    const unsigned long long *keys = from_raw ? w.raw.as<unsigned long long>() : w.uniq.as<unsigned long long>();
+    const unsigned long long *n_keys = from_raw ? &w.ctr.as<ScanCounters>()->n_raw : n_unique;
+    const uint64_t key_cap = from_raw ? std::min<uint64_t>(w.raw_cap, kSmallSort) : w.ev_cap;
+    CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), keys, n_keys, key_cap,
+                      w.uniq.as<unsigned long long>(), n_unique, w.ev_cap, L.on(w.ev_soa.p), rs, d->num_sms, w.stream, w.stream2, w.fork_ev[1],
+                      w.join_ev[1], from_raw ? w.join_ev[2] : nullptr));
     w.launches += 4;
     w.mark("resolve (plan,check,finalize)");
     CU(cudaEventRecord(w.e[6], w.stream));
@@ -577,17 +587,21 @@ int scan_async(pm_batch *b) {
             w.launches++;
         }
         CU(cudaEventRecord(w.e[9], w.stream));
+        // ordering and de-duplication run beside plan/check (which take the raw queue as it is);
+        // k_finalize waits for them and places each row at its key's rank
+        CU(cudaEventRecord(w.fork_ev[2], w.stream));
+        CU(cudaStreamWaitEvent(w.stream3, w.fork_ev[2], 0));
         CU(launch_sort_small(w.raw.as<unsigned long long>(), w.ctr.as<ScanCounters>(), w.raw_cap, w.sort_scratch.as<unsigned long long>(),
                              w.uniq.as<unsigned long long>(),
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
-                             reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream));
+                             reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream3));
+        CU(cudaEventRecord(w.join_ev[2], w.stream3));
         w.launches += 3;
-        w.mark("sort");
         CU(cudaStreamWaitEvent(w.stream, w.join_ev[0], 0));
         w.mark("join prefix/pods");
         CU(cudaEventRecord(w.e[4], w.stream));
         CU(cudaEventRecord(w.e[5], w.stream));
-        if ((rc = enqueue_resolve(b, w))) return rc;
+        if ((rc = enqueue_resolve(b, w, true))) return rc;
     }
     return PM_OK;
 }
