@@ -15,9 +15,9 @@
  *   - buffers that cross the ABI are owned by the C side (pm_host_alloc / result views);
  *     the caller never frees anything but through the matching pm_* call;
  *   - pm_ctx and a published pm_library are thread-safe; a pm_batch belongs to one thread;
- *   - a device runs one batch at a time: pm_batch_stage/submit block while another batch holds the
- *     device and until that batch is released (so release a batch before the same thread stages
- *     the next one on the same devices);
+ *   - a device holds one batch at a time unless pm_set_pipeline raised that: pm_batch_stage/submit
+ *     block while the device is full and until a batch holding it is released (so release a batch
+ *     before the same thread stages one more than the depth on the same devices);
  *   - there is no CPU fallback: without a usable CUDA device pm_init fails.
  */
 #ifndef PODMORTEM_SCAN_H
@@ -111,6 +111,17 @@ int pm_init_devices(const int *device_ids, int n, pm_ctx **out);
 void pm_shutdown(pm_ctx *);
 const char *pm_last_error(void);
 int pm_device_count(const pm_ctx *);
+/* Batches in flight per device.  depth 1 (the default): a device runs one batch at a time and every
+ * kernel may use all of its SMs - the lowest latency for a single request.  depth 2..8: up to
+ * `depth` batches hold a device at once and its SMs are split into two green contexts (driver API,
+ * CUDA >= 12.4): the filter kernel of one batch streams on all but ~post_sms SMs while the
+ * latency-bound confirm/sort/resolve tail of the batches before it runs on the rest - the
+ * throughput mode of a service with requests queued (pm_batch_submit on several batches, then
+ * pm_batch_wait in submission order).  The driver rounds post_sms up to its partition granularity;
+ * the SM counts actually given to the two partitions of the first device are returned through
+ * scan_sms / post_sms_actual (either may be NULL).  Call it with no batch staged.  No counterpart in
+ * the reference (its /parse service handles one request per thread). */
+int pm_set_pipeline(pm_ctx *, int depth, int post_sms, int *scan_sms, int *post_sms_actual);
 
 /* ---- pattern library (a9; PatternSyncService.java:42-77 hands the files over) ---------- */
 /* spec: UTF-8 JSON, one library object or an array of them (SPEC.md s.1). */

@@ -69,7 +69,7 @@ ABI_SYMBOLS = ["pm_abi_version", "pm_init", "pm_init_devices", "pm_shutdown", "p
                "pm_library_publish", "pm_library_free", "pm_library_pattern_count", "pm_library_pattern_meta_json",
                "pm_host_alloc", "pm_host_free", "pm_batch_begin", "pm_batch_add_pod", "pm_batch_submit", "pm_batch_wait",
                "pm_batch_release", "pm_batch_stage", "pm_batch_rescan", "pm_batch_line_index", "pm_parse",
-               "pm_line_index_noalloc", "pm_noalloc_last_error"]
+               "pm_line_index_noalloc", "pm_noalloc_last_error", "pm_set_pipeline"]
 
 
 def load_library() -> ctypes.CDLL:
@@ -108,6 +108,7 @@ def load_library() -> ctypes.CDLL:
     d.pm_batch_release.restype = None
     d.pm_batch_stage.argtypes = [vp]
     d.pm_batch_rescan.argtypes = [vp, _P(ResultView)]
+    d.pm_set_pipeline.argtypes = [vp, ctypes.c_int, ctypes.c_int, _P(ctypes.c_int), _P(ctypes.c_int)]
     d.pm_batch_line_index.argtypes = [vp, ctypes.c_int, _P(ctypes.c_int64), ctypes.c_int64]
     d.pm_batch_line_index.restype = ctypes.c_int64
     d.pm_parse.argtypes = [vp, ctypes.c_char_p, sz, _P(ctypes.c_char_p), _P(sz)]
@@ -266,6 +267,13 @@ class Engine:
     @property
     def device_count(self) -> int:
         return load_library().pm_device_count(self._ctx)
+
+    def set_pipeline(self, depth: int, post_sms: int = 16):
+        """Batches in flight per device (pm_set_pipeline).  Returns (scan_sms, post_sms) of the
+        partition the driver made; depth 1 goes back to one batch per device on all SMs."""
+        a, b = ctypes.c_int(0), ctypes.c_int(0)
+        _check(load_library().pm_set_pipeline(self._ctx, depth, post_sms, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
 
     def compile_library(self, spec: Union[dict, list, str, bytes]) -> Library:
         """a9: library JSON (SPEC.md section 1) -> compiled tables.  Raises ScanError carrying the

@@ -98,3 +98,59 @@ def test_crash_storm_many_small_pods(engine):
                 for e in oracle.analyze(bytes(pods[k]), olib)]
         assert _got(res, int(k)) == want, k
         assert int(res.pod_n_lines[k]) == len(oracle.split_lines(bytes(pods[k])))
+
+
+_PIPE = r"""
+import sys, threading
+sys.path.insert(0, %r)
+import numpy as np
+from operator_b200 import Engine, ScanError, synth
+from oracle import oracle
+lib_json, wit, swit = synth.make_library(50)
+logs = [synth.make_corpus(700000 + 90000 * k, wit, swit, p_hit=2e-2, seed=100 + k)[0] for k in range(4)]
+olib = oracle.load_library(lib_json)
+want = [[(e.line_no, e.pattern, e.ctx_first, e.ctx_last, e.score) for e in oracle.analyze(bytes(l), olib)] for l in logs]
+def rows(res, pod=0):
+    return [(g["line_no"], g["pattern"], g["ctx_first"], g["ctx_last"], g["score"]) for g in res.events_of(pod)]
+eng = Engine(1)
+eng.compile_library(lib_json).publish()
+for depth, post in ((3, 0), (2, 16), (1, 0)):
+    sms = eng.set_pipeline(depth, post)
+    if post:
+        assert 0 < sms[1] < sms[0] and sms[0] + sms[1] <= 160, sms
+    # several batches submitted before the first wait, re-submitted while others are in flight
+    batches = []
+    for k in range(depth):
+        b = eng.batch(); b.add_pod(logs[k], k); b.stage(); batches.append(b)
+    for rounds in range(3):
+        for b in batches: b.submit()
+        for k, b in enumerate(batches):
+            got = rows(b.wait())
+            assert got == want[k] and len(got) > 20, (depth, post, rounds, k, len(got), len(want[k]))
+    if depth > 1:
+        try:
+            eng.set_pipeline(1, 0)
+            raise SystemExit("set_pipeline with batches staged must fail")
+        except ScanError:
+            pass
+    for b in batches: b.release()
+    # threads, one request each, all at once (the /parse service shape)
+    out = [None] * 4
+    def work(k):
+        out[k] = rows(eng.scan([logs[k]]))
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+    for t in ts: t.start()
+    for t in ts: t.join()
+    assert out == want, (depth, post)
+eng.close()
+print("pipeline ok")
+"""
+
+
+def test_batches_in_flight_share_a_device(tmp_path):
+    """pm_set_pipeline: depth 3 on shared SMs, depth 2 on a green-context SM split, back to depth 1;
+    interleaved submits/waits and concurrent threads give the oracle's events every time."""
+    script = tmp_path / "pipe.py"
+    script.write_text(_PIPE % ROOT)
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "pipeline ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
