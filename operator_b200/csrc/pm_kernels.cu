@@ -507,18 +507,116 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
     }
 }
 
+// One warp walks one line [a, b) through a unit DFA and returns the state after the last byte
+// (END-OF-LINE not yet fed), or `acc` / `dead` as soon as one of them is reached (accepting is
+// sticky, dead is absorbing).  A walk is a chain of dependent table lookups, so everything that
+// does not depend on the state is taken off the chain first: the warp loads the line 512 bytes at
+// a time (16 aligned bytes per lane), maps the bytes to character classes in parallel and leaves
+// the classes in shared memory.  What remains per byte is one shared-memory read that can be
+// issued ahead and one table read through L1 (the caller has touched the table's cache lines, see
+// warp_touch_table: a line meets its pattern's table for the first time, and an L1 miss in the
+// chain costs ~300 ns).
+//   - pieces up to kWalkSerial bytes: every lane runs the same chain (broadcast reads, no divergence);
+//   - longer pieces: lane i guesses the state at the start of its 1/32 of the piece (the DFA's
+//     mid-line idle state warmed up over the 16 bytes in front), the guesses are validated in lane
+//     order and a wrong one re-walks that chunk from the true state: exact, and on text that
+//     leaves the DFA idle ~16x shorter than the serial chain.  Matching lines do not leave the DFA
+//     idle (after the first half of "A.*B" every later guess is wrong), which is why short lines,
+//     the common case, are not speculated on at all.
+// gcm: the unit's 256-byte class map (global); cmap_s / cls: 256 / kWalkPiece bytes of shared
+// memory owned by the warp.
+constexpr uint32_t kWalkPiece = 512, kWalkSerial = 192;
+
+// Brings a table of `bytes` bytes into L1 with one load per 32-byte sector (L1 fills sector by
+// sector), all of them in flight at once.
+__device__ __forceinline__ void warp_touch_table(const uint16_t *tab, uint32_t bytes) {
+    const int lane = threadIdx.x & 31;
+    const uint8_t *base = reinterpret_cast<const uint8_t *>(tab);
+    uint32_t sink = 0;
+#pragma unroll 4
+    for (uint32_t off = lane * 32u; off < bytes; off += 32u * 32u) sink ^= __ldg(reinterpret_cast<const uint32_t *>(base + off));
+    asm volatile("" ::"r"(sink));   // keeps the loads; nothing waits for them here
+}
+
+__device__ __forceinline__ uint32_t warp_walk_line(const uint8_t *__restrict__ text, unsigned long long a, unsigned long long b, const uint16_t *__restrict__ tab,
+                                                   uint32_t stride, uint32_t acc, uint32_t dead, uint32_t mid, const uint8_t *__restrict__ gcm,
+                                                   uint8_t *cmap_s, uint8_t *cls) {
+    const int lane = threadIdx.x & 31;
+    uint32_t s = 0;
+    auto walk = [&](uint32_t s0, uint32_t p0, uint32_t p1) {
+        uint32_t k = p0;
+        for (; k + 4 <= p1 && s0 != acc && s0 != dead; k += 4) {
+            const uint32_t c0 = cls[k], c1 = cls[k + 1], c2 = cls[k + 2], c3 = cls[k + 3];
+            s0 = __ldg(tab + s0 * stride + c0);
+            s0 = __ldg(tab + s0 * stride + c1);
+            s0 = __ldg(tab + s0 * stride + c2);
+            s0 = __ldg(tab + s0 * stride + c3);
+        }
+        for (; k < p1 && s0 != acc && s0 != dead; k++) s0 = __ldg(tab + s0 * stride + cls[k]);
+        return s0;
+    };
+    bool have_cmap = false;
+    for (unsigned long long base = a & ~15ull; base < b && s != acc && s != dead; base += kWalkPiece) {
+        __syncwarp();
+        const unsigned long long mine = base + 16ull * lane;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (mine < b) v = *reinterpret_cast<const uint4 *>(text + mine);
+        if (!have_cmap) {   // the class map travels together with the first piece of the line
+            const uint32_t m0 = __ldg(reinterpret_cast<const uint32_t *>(gcm) + lane), m1 = __ldg(reinterpret_cast<const uint32_t *>(gcm) + 32 + lane);
+            reinterpret_cast<uint32_t *>(cmap_s)[lane] = m0;
+            reinterpret_cast<uint32_t *>(cmap_s)[32 + lane] = m1;
+            have_cmap = true;
+            __syncwarp();
+        }
+        if (mine < b) {
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                o[q] = (uint32_t)cmap_s[w[q] & 0xFFu] | ((uint32_t)cmap_s[(w[q] >> 8) & 0xFFu] << 8) | ((uint32_t)cmap_s[(w[q] >> 16) & 0xFFu] << 16) |
+                       ((uint32_t)cmap_s[w[q] >> 24] << 24);
+            *reinterpret_cast<uint4 *>(cls + 16 * lane) = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+        __syncwarp();
+        const uint32_t lo = a > base ? (uint32_t)(a - base) : 0u;
+        const uint32_t hi = b - base < kWalkPiece ? (uint32_t)(b - base) : kWalkPiece;
+        const uint32_t n = hi - lo;
+        if (n <= kWalkSerial) {
+            s = walk(s, lo, hi);
+            continue;
+        }
+        const uint32_t c = (n + 31) / 32;
+        const uint32_t ca = min(hi, lo + lane * c), cb = min(hi, ca + c);
+        const uint32_t in_spec = (lane == 0 || ca - lo <= 16) ? walk(s, lo, ca) : walk(mid, ca - 16, ca);
+        const uint32_t out_spec = walk(in_spec, ca, cb);
+        uint32_t truth = s;   // true state at the start of chunk i
+        for (int i = 0; i < 32; i++) {
+            uint32_t in_i = __shfl_sync(FULL, in_spec, i), out_i = __shfl_sync(FULL, out_spec, i);
+            if (i > 0 && in_i != truth) {   // warp-uniform; chunk 0 starts from the true state by construction
+                uint32_t redo = 0;
+                if (lane == i) redo = walk(truth, ca, cb);
+                out_i = __shfl_sync(FULL, redo, i);
+            }
+            truth = out_i;
+            if (truth == acc || truth == dead) break;
+        }
+        s = truth;
+    }
+    __syncwarp();
+    return s;
+}
+
 // Stage 2: one warp per verify task.  The chain "find the line, fetch the pattern's tables, walk
 // the line" is a string of dependent cache misses when one thread does it byte by byte, so the
 // warp fetches in bulk instead: 512 bytes around the literal in one round trip (newline search by
-// ballot), the pattern's class map and table into shared memory, the line into shared memory;
-// lane 0 then walks the DFA out of shared memory.
-constexpr int kVerifyWarps = 4, kVerifyLine = 512;
+// ballot), the pattern's class map into shared memory, then warp_walk_line.
+constexpr int kVerifyWarps = 4;
 
-__global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h, PodTable pt,
+__global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h, PodTable pt,
                                                               const unsigned long long *__restrict__ tasks, unsigned long long task_cap,
                                                               unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
     __shared__ __align__(16) uint8_t s_cmap[kVerifyWarps][256];
-    __shared__ __align__(16) uint8_t s_line[kVerifyWarps][kVerifyLine];
+    __shared__ __align__(16) uint8_t s_cls[kVerifyWarps][kWalkPiece];
     if (ctr->cand_overflow || ctr->raw_overflow) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned long long n = ctr->n_verified < task_cap ? ctr->n_verified : task_cap;
@@ -527,12 +625,16 @@ __global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__r
     for (unsigned long long i = (unsigned long long)blockIdx.x * kVerifyWarps + warp; i < n; i += n_warps) {
         const unsigned long long t = tasks[i], p = t >> kPatternBits;
         const uint32_t pat = (uint32_t)(t & ((1u << kPatternBits) - 1u));
-        const UnitDesc ud = reinterpret_cast<const UnitDesc *>(blob + h.off_units)[pd[pat].unit];
-        // ---- line bounds: 16 lanes look back, 16 lanes look ahead, 256 bytes each, one round trip
+        // ---- line bounds: 16 lanes look back, 16 lanes look ahead, 256 bytes each, one round trip;
+        //      the pattern's descriptors are fetched under it, and the table's lines after them
         const unsigned long long p16 = p & ~15ull;
         unsigned long long a = lane < 16 ? p16 - 16ull * (lane + 1) : p16 + 16ull * (lane - 16);
-        uint32_t m = 0;
-        if (lane >= 16 || p16 >= 16ull * (lane + 1)) m = newline_mask16(*reinterpret_cast<const uint4 *>(text + a));
+        uint4 around = make_uint4(0x20202020u, 0x20202020u, 0x20202020u, 0x20202020u);
+        if (lane >= 16 || p16 >= 16ull * (lane + 1)) around = *reinterpret_cast<const uint4 *>(text + a);
+        const UnitDesc ud = reinterpret_cast<const UnitDesc *>(blob + h.off_units)[pd[pat].unit];
+        const uint16_t *gtab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off;
+        warp_touch_table(gtab, (uint32_t)ud.nstates * ud.stride * 2u);
+        uint32_t m = newline_mask16(around);
         if (lane == 16) m &= ~((1u << (p - p16)) - 1u);          // forward search starts at p
         unsigned has = __ballot_sync(FULL, m != 0);
         unsigned long long ls, le;
@@ -541,9 +643,18 @@ __global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__r
             int src = 16 + __ffs(fwd) - 1;
             uint32_t mm = __shfl_sync(FULL, m, src);
             le = p16 + 16ull * (src - 16) + (__ffs(mm) - 1);
-        } else {
-            le = p16 + 256;
-            while (text[le] != '\n') le++;
+        } else {   // a long line: keep looking, 512 bytes per round trip (the text is '\n'-padded up to `total`)
+            le = total;
+            for (unsigned long long q = p16 + 256; q < total; q += 512) {
+                const unsigned long long mine = q + 16ull * lane;
+                const uint32_t mq = mine < total ? newline_mask16(*reinterpret_cast<const uint4 *>(text + mine)) : 0u;
+                const unsigned hq = __ballot_sync(FULL, mq != 0);
+                if (hq) {
+                    const int src = __ffs(hq) - 1;
+                    le = q + 16ull * src + (__ffs(__shfl_sync(FULL, mq, src)) - 1);
+                    break;
+                }
+            }
         }
         // backward: the nearest newline strictly before p (bytes of p16's own chunk below p belong to lane 16's chunk)
         uint32_t m_own = __shfl_sync(FULL, lane == 16 ? newline_mask16(*reinterpret_cast<const uint4 *>(text + p16)) & ((1u << (p - p16)) - 1u) : 0u, 16);
@@ -554,54 +665,23 @@ __global__ void __launch_bounds__(kVerifyWarps * 32) k_verify(const uint8_t *__r
             uint32_t mm = __shfl_sync(FULL, m, src);
             ls = p16 - 16ull * (src + 1) + (31 - __clz(mm)) + 1;
         } else {
-            ls = p16 >= 256 ? p16 - 256 : 0;
-            while (ls > 0 && text[ls - 1] != '\n') ls--;
+            ls = 0;
+            for (unsigned long long q = p16 >= 256 ? p16 - 256 : 0; q > 0; q = q >= 512 ? q - 512 : 0) {   // q: exclusive upper end, 16-aligned
+                const uint32_t mq = q >= 16ull * (lane + 1) ? newline_mask16(*reinterpret_cast<const uint4 *>(text + q - 16ull * (lane + 1))) : 0u;
+                const unsigned hq = __ballot_sync(FULL, mq != 0);
+                if (hq) {
+                    const int src = __ffs(hq) - 1;                   // lane 0 holds the nearest chunk
+                    ls = q - 16ull * (src + 1) + (31 - __clz(__shfl_sync(FULL, mq, src))) + 1;
+                    break;
+                }
+            }
         }
         const unsigned long long lend = strip_cr(text, pt, ls, le);
-        const unsigned long long len = lend - ls;
-        // ---- stage tables and line
-        const uint16_t *gtab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off;
-        const uint8_t *gcm = blob + h.off_classmaps + ud.classmap_off;
-        const bool line_fits = len <= kVerifyLine;
-        __syncwarp();
-        for (int k = lane; k < 256 / 4; k += 32) reinterpret_cast<uint32_t *>(s_cmap[warp])[k] = reinterpret_cast<const uint32_t *>(gcm)[k];
-        if (line_fits)
-            for (unsigned long long k = lane; k < len; k += 32) s_line[warp][k] = text[ls + k];
-        __syncwarp();
-        uint32_t st = 0;
-        const uint32_t stride = ud.stride, acc = ud.accept_state, dead = ud.dead_state;
-        if (line_fits) {
-            // Line and class map are in shared memory, the table is read through L1.  All 32 lanes walk: lane i takes bytes [i*c, (i+1)*c) from a
-            // guessed entry state (mid-line idle state warmed up over the 16 bytes in front of its
-            // piece), then the guesses are validated in lane order and a wrong one is redone -- the
-            // speculation of k_check_long, here to cut the serial chain of a ~140-byte line to ~20 steps.
-            const uint16_t *tab = gtab;
-            const uint8_t *cm = s_cmap[warp], *ln = s_line[warp];
-            const uint32_t n32 = (uint32_t)len, c = (n32 + 31) / 32;
-            const uint32_t ca = min(n32, lane * c), cb = min(n32, ca + c);
-            auto walk = [&](uint32_t s0, uint32_t p0, uint32_t p1) {
-                for (uint32_t k = p0; k < p1 && s0 != acc && s0 != dead; k++) s0 = tab[s0 * stride + cm[ln[k]]];
-                return s0;
-            };
-            const uint32_t in_spec = (lane == 0 || ca <= 16) ? walk(0, 0, ca) : walk(ud.mid_state, ca - 16, ca);
-            const uint32_t out_spec = walk(in_spec, ca, cb);
-            uint32_t truth = 0;
-            for (int i = 0; i < 32; i++) {
-                uint32_t in_i = __shfl_sync(FULL, in_spec, i), out_i = __shfl_sync(FULL, out_spec, i);
-                if (in_i != truth) {   // warp-uniform
-                    uint32_t redo = 0;
-                    if (lane == i) redo = walk(truth, ca, cb);
-                    out_i = __shfl_sync(FULL, redo, i);
-                }
-                truth = out_i;
-                if (truth == acc || truth == dead) break;
-            }
-            st = truth;
-            if (st != acc) st = tab[st * stride + stride - 1];
-        } else if (lane == 0) {
-            for (unsigned long long k = ls; k < lend && st != acc && st != dead; k++) st = gtab[st * stride + gcm[text[k]]];
-            if (st != acc) st = gtab[st * stride + stride - 1];
-        }
+        // ---- the walk (class map and first piece of the line travel together)
+        const uint32_t stride = ud.stride, acc = ud.accept_state;
+        uint32_t st = warp_walk_line(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, blob + h.off_classmaps + ud.classmap_off,
+                                     s_cmap[warp], s_cls[warp]);
+        if (st != acc) st = __ldg(gtab + st * stride + stride - 1);
         if (lane == 0) {
             if (st == acc) {
                 unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
@@ -1512,7 +1592,7 @@ cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, 
                            int num_sms, cudaStream_t s) {
     if (lib.fv.log2_bits == 0) return cudaSuccess;
     k_confirm<<<num_sms * 8, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
-    k_verify<<<num_sms * 16, kVerifyWarps * 32, 0, s>>>(text, lib.blob, lib.h, pt, tasks, raw_cap, raw, raw_cap, ctr);
+    k_verify<<<num_sms * 16, kVerifyWarps * 32, 0, s>>>(text, total_bytes, lib.blob, lib.h, pt, tasks, raw_cap, raw, raw_cap, ctr);
     return cudaGetLastError();
 }
 

@@ -185,3 +185,9 @@ const char *pmt_literals(pmt_lib *l, int p) {
 }
 
 }  // extern "C"
+
+// Transition-table entries (states x columns) of a pattern's verify DFA.
+extern "C" int pmt_unit_table_entries(pmt_lib *l, int p) {
+    const pm::Dfa &d = l->lib.unit_dfas[pdesc(l)[p].unit];
+    return d.nstates * d.stride();
+}

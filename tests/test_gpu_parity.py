@@ -292,3 +292,40 @@ def test_tier2_dfa_multi_tile(engine):
     lf = synth.make_corpus(24 << 20, wit, swit, p_hit=1e-3)[0]
     crlf = synth.make_corpus(3 << 20, wit, swit, p_hit=1e-3, crlf=True, first_line=10 ** 7)[0]
     check_parity(engine, lib_json, [lf, crlf], expect_events=5000)
+
+
+def test_long_lines_through_verify_and_context(engine):
+    """Lines of 0.2-9 KB with the literal at the start, in the middle, at the end and across the
+    512-byte pieces of the warp walk; 'A.*B' regexes whose two halves are KBs apart (every
+    speculative guess after A is wrong and is redone); long lines as context and secondary lines."""
+    regs = [r"OutOfMemoryError: Java heap", r"fatal-alpha.*omega-done", r"^START-OF-LINE \w+ .*tail-marker$",
+            r"(?i)connection refused by PEER \d+", r"begin-xyz\d+.*mid-xyz.*end-xyz"]
+    lib = lib_of(regs, context_extraction={"lines_before": 2, "lines_after": 3, "include_stack_trace": True})
+    lib["patterns"][0]["secondary_patterns"] = [{"regex": r"GC overhead", "weight": 0.4, "proximity_window": 4},
+                                                 {"regex": r"payload-\w+-end", "weight": 0.3, "proximity_window": 6}]
+    rng = np.random.default_rng(7)
+
+    def filler(n):
+        words = [b"alpha", b"beta", b"{\"k\":\"0123456789abcdef\"}", b"GC", b"overhead?", b"at", b"java.base/Thread.run", b"fatal", b"omega"]
+        out = bytearray()
+        while len(out) < n:
+            out += words[int(rng.integers(len(words)))] + b" "
+        return bytes(out[:n])
+
+    lines = []
+    for n in (10, 150, 200, 500, 511, 512, 513, 700, 1024, 2000, 4093, 9000):
+        lines.append(b"OutOfMemoryError: Java heap " + filler(n))
+        lines.append(filler(n) + b" OutOfMemoryError: Java heap")
+        lines.append(filler(n // 2) + b" OutOfMemoryError: Java heap " + filler(n // 2))
+        lines.append(b"fatal-alpha " + filler(n) + b" omega-done")
+        lines.append(b"fatal-alpha " + filler(n))                       # first half only: no match
+        lines.append(b"START-OF-LINE word " + filler(n) + b" tail-marker")
+        lines.append(b"xSTART-OF-LINE word " + filler(n) + b" tail-marker")
+        lines.append(filler(n) + b" Connection Refused by peer 42 " + filler(7))
+        lines.append(b"begin-xyz7 " + filler(n) + b" mid-xyz " + filler(n) + b" end-xyz")
+        lines.append(b"\tat " + filler(n))                                 # stack-like context line
+        lines.append(b"GC overhead limit " + filler(n) + b" payload-abc-end")
+        lines.append(filler(40))
+    log = b"\n".join(lines) + b"\n"
+    res = check_parity(engine, lib, [log, log[:len(log) // 2], b"\r\n".join(lines)])
+    assert res.n_events > 100
