@@ -187,6 +187,10 @@ const char *pm_noalloc_last_error(void);
  * an AnalysisResult JSON document owned by the context, valid until the next pm_parse on the
  * same thread. */
 int pm_parse(pm_ctx *, const uint8_t *request_json, size_t n, const char **response, size_t *response_len);
+/* Concurrent pm_parse calls are coalesced into shared GPU batches (one pod per request; SURVEY.md
+ * section 8(f).1 - the reference sends one pod per request, PodFailureWatcher.java:196-199).  Requests
+ * served so far, the batches they were served in, and the largest batch; any pointer may be NULL. */
+int pm_parse_stats(pm_ctx *, int64_t *requests, int64_t *batches, int64_t *largest_batch);
 
 #ifdef __cplusplus
 }

@@ -182,6 +182,8 @@ struct pm_ctx {
     std::mutex mu;
     pm_library *current = nullptr;
     DriverApi drv;
+    void *service_state = nullptr;             // owned by pm_service.cc
+    void (*service_deleter)(void *) = nullptr;
     std::mutex user_pinned_mu;
     std::map<void *, size_t> user_pinned;
     std::string parse_response;   // see pm_service.cc
@@ -959,6 +961,7 @@ int pm_init(int n_devices, pm_ctx **out) {
 
 void pm_shutdown(pm_ctx *ctx) {
     if (!ctx) return;
+    if (ctx->service_state && ctx->service_deleter) ctx->service_deleter(ctx->service_state);
     if (ctx->current) lib_unref(ctx->current);
     for (auto *d : ctx->devs) {
         cudaSetDevice(d->id);
@@ -1233,4 +1236,15 @@ void *ctx_pinned_get(pm_ctx *ctx, size_t bytes, size_t *cap) {
     return p;
 }
 void ctx_pinned_put(pm_ctx *ctx, void *p, size_t cap) { ctx->pinned.put(p, cap); }
+// pm_service.cc keeps its request batcher here; the deleter runs in pm_shutdown.
+void *&ctx_service_state(pm_ctx *ctx) { return ctx->service_state; }
+void (*&ctx_service_deleter(pm_ctx *ctx))(void *) { return ctx->service_deleter; }
+std::mutex &ctx_mutex(pm_ctx *ctx) { return ctx->mu; }
+int ctx_pipeline_depth(pm_ctx *ctx) { return ctx->devs.empty() ? 1 : ctx->devs[0]->depth; }
+pm_library *batch_library_addref(pm_batch *b) {
+    if (b->lib) b->lib->refs.fetch_add(1);
+    return b->lib;
+}
+void library_release(pm_library *l) { lib_unref(l); }
+void set_thread_error(const char *msg) { g_err = msg ? msg : ""; }
 }  // namespace pm

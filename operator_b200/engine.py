@@ -69,7 +69,7 @@ ABI_SYMBOLS = ["pm_abi_version", "pm_init", "pm_init_devices", "pm_shutdown", "p
                "pm_library_publish", "pm_library_free", "pm_library_pattern_count", "pm_library_pattern_meta_json",
                "pm_host_alloc", "pm_host_free", "pm_batch_begin", "pm_batch_add_pod", "pm_batch_submit", "pm_batch_wait",
                "pm_batch_release", "pm_batch_stage", "pm_batch_rescan", "pm_batch_line_index", "pm_parse",
-               "pm_line_index_noalloc", "pm_noalloc_last_error", "pm_set_pipeline"]
+               "pm_line_index_noalloc", "pm_noalloc_last_error", "pm_set_pipeline", "pm_parse_stats"]
 
 
 def load_library() -> ctypes.CDLL:
@@ -108,6 +108,7 @@ def load_library() -> ctypes.CDLL:
     d.pm_batch_release.restype = None
     d.pm_batch_stage.argtypes = [vp]
     d.pm_batch_rescan.argtypes = [vp, _P(ResultView)]
+    d.pm_parse_stats.argtypes = [vp, _P(ctypes.c_int64), _P(ctypes.c_int64), _P(ctypes.c_int64)]
     d.pm_set_pipeline.argtypes = [vp, ctypes.c_int, ctypes.c_int, _P(ctypes.c_int), _P(ctypes.c_int)]
     d.pm_batch_line_index.argtypes = [vp, ctypes.c_int, _P(ctypes.c_int64), ctypes.c_int64]
     d.pm_batch_line_index.restype = ctypes.c_int64
@@ -314,6 +315,17 @@ class Engine:
         out, n = ctypes.c_char_p(), ctypes.c_size_t()
         _check(load_library().pm_parse(self._ctx, failure_data, len(failure_data), ctypes.byref(out), ctypes.byref(n)))
         return json.loads(ctypes.string_at(out, n.value).decode("utf-8"))
+
+    def parse_raw(self, body: bytes) -> bytes:
+        """pm_parse without the Python-side JSON decode (what an HTTP front end forwards)."""
+        out, n = ctypes.c_char_p(), ctypes.c_size_t()
+        _check(load_library().pm_parse(self._ctx, body, len(body), ctypes.byref(out), ctypes.byref(n)))
+        return ctypes.string_at(out, n.value)
+
+    def parse_stats(self) -> dict:
+        a, b, c = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int64()
+        _check(load_library().pm_parse_stats(self._ctx, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return {"requests": a.value, "batches": b.value, "largest_batch": c.value}
 
     def close(self):
         if self._ctx:

@@ -329,3 +329,47 @@ def test_long_lines_through_verify_and_context(engine):
     log = b"\n".join(lines) + b"\n"
     res = check_parity(engine, lib, [log, log[:len(log) // 2], b"\r\n".join(lines)])
     assert res.n_events > 100
+
+
+def test_concurrent_parse_requests_share_batches(engine):
+    """8(f).1: many /parse calls at once (one pod per request, as the operator sends them) are
+    coalesced into shared GPU batches; every caller gets exactly the answer of a call made alone."""
+    import json
+    import threading
+    lib_json, wit, swit = synth.make_library(50)
+    engine.compile_library(lib_json).publish()
+    olib = oracle.load_library(lib_json)
+    n = 24
+    logs = [bytes(synth.make_corpus(60000 + 7000 * k, wit, swit, p_hit=3e-2, seed=900 + k)[0]) for k in range(n)]
+    logs[5] = b""                                        # an empty log rides along
+    bodies = [json.dumps({"pod": {"metadata": {"name": "pod-%d" % k, "namespace": "ns"}}, "logs": l.decode(), "events": []}).encode()
+              for k, l in enumerate(logs)]
+    before = engine.parse_stats()
+    out = [None] * n
+    gate = threading.Barrier(n)
+
+    def work(k):
+        gate.wait()
+        for _ in range(3):
+            out[k] = json.loads(engine.parse_raw(bodies[k]))
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(n)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    after = engine.parse_stats()
+    assert after["requests"] - before["requests"] == 3 * n
+    assert after["batches"] - before["batches"] < 3 * n, after        # at least some requests shared a batch
+    assert after["largest_batch"] >= 2
+    for k in range(n):
+        ev = oracle.analyze(logs[k], olib)
+        assert out[k]["metadata"]["podName"] == "pod-%d" % k
+        assert [(o["lineNumber"], o["matchedPattern"]["id"], o["score"]) for o in out[k]["events"]] == \
+               [(e.line_no, olib.patterns[e.pattern].id, e.score) for e in ev], k
+        lines = logs[k].decode().split("\n")
+        for o, e in zip(out[k]["events"], ev):
+            assert o["context"]["matchedLine"] == lines[e.line_no - 1]
+            assert o["context"]["linesAfter"] == lines[e.line_no:e.ctx_last]
+        assert out[k]["summary"]["totalEvents"] == len(ev)
+    assert sum(len(o["events"]) for o in out) > 200
