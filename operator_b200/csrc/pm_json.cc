@@ -203,6 +203,22 @@ bool json_parse(const char *data, size_t n, JsonValue &out, std::string &err, si
     return ok;
 }
 
+// Index of the quote that closes the string whose first content byte is s[j] (n if there is none).
+// memchr does the walking: a quote is real when an even number of backslashes stands before it.
+static size_t string_end(const char *s, size_t n, size_t j) {
+    const size_t first = j;
+    while (j < n) {
+        const char *q = static_cast<const char *>(memchr(s + j, '"', n - j));
+        if (!q) return n;
+        const size_t e = (size_t)(q - s);
+        size_t k = e;
+        while (k > first && s[k - 1] == '\\') k--;
+        if (((e - k) & 1) == 0) return e;
+        j = e + 1;
+    }
+    return n;
+}
+
 bool json_find_top_level_string(const char *s, size_t n, const char *key, size_t *begin, size_t *end) {
     const size_t klen = strlen(key);
     int depth = 0;
@@ -211,8 +227,7 @@ bool json_find_top_level_string(const char *s, size_t n, const char *key, size_t
     while (i < n) {
         char c = s[i];
         if (c == '"') {
-            size_t j = i + 1;
-            while (j < n && s[j] != '"') j += (s[j] == '\\' && j + 1 < n) ? 2 : 1;
+            const size_t j = string_end(s, n, i + 1);
             if (j >= n) return false;
             if (depth == 1 && expect_key) {
                 bool is_key = (j - i - 1 == klen) && !memcmp(s + i + 1, key, klen);
@@ -223,8 +238,7 @@ bool json_find_top_level_string(const char *s, size_t n, const char *key, size_t
                     while (k < n && (s[k] == ' ' || s[k] == '\t' || s[k] == '\n' || s[k] == '\r')) k++;
                     if (is_key) {
                         if (k >= n || s[k] != '"') return false;
-                        size_t e = k + 1;
-                        while (e < n && s[e] != '"') e += (s[e] == '\\' && e + 1 < n) ? 2 : 1;
+                        const size_t e = string_end(s, n, k + 1);
                         if (e >= n) return false;
                         *begin = k + 1;
                         *end = e;

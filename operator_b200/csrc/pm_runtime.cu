@@ -114,6 +114,34 @@ struct Device {
     // verify, sort, resolve) of the previous batch runs on the other sms_post.
     CUgreenCtx gc_scan = nullptr, gc_post = nullptr;
     int sms_scan = 0, sms_post = 0;
+    // Streams and events of finished batches, kept for the next one: creating three streams and
+    // sixteen events costs more host time than a 1 MB request spends on the GPU.
+    struct StreamSet {
+        cudaStream_t stream = nullptr, stream2 = nullptr, stream3 = nullptr, scan_stream = nullptr;
+        cudaEvent_t scan_fork = nullptr, scan_join = nullptr, fork_ev[3] = {nullptr, nullptr, nullptr}, join_ev[3] = {nullptr, nullptr, nullptr};
+        cudaEvent_t e[10] = {nullptr};
+        void destroy() {
+            for (cudaStream_t *st : {&stream, &stream2, &stream3, &scan_stream})
+                if (*st) cudaStreamDestroy(*st), *st = nullptr;
+            for (cudaEvent_t *ev : {&scan_fork, &scan_join})
+                if (*ev) cudaEventDestroy(*ev), *ev = nullptr;
+            for (int k = 0; k < 3; k++) {
+                if (fork_ev[k]) cudaEventDestroy(fork_ev[k]), fork_ev[k] = nullptr;
+                if (join_ev[k]) cudaEventDestroy(join_ev[k]), join_ev[k] = nullptr;
+            }
+            for (auto &ev : e)
+                if (ev) cudaEventDestroy(ev), ev = nullptr;
+        }
+    };
+    std::vector<StreamSet> idle_sets;   // guarded by mu; emptied when the pipeline mode changes
+    void drop_idle_sets() {
+        std::vector<StreamSet> sets;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            sets.swap(idle_sets);
+        }
+        for (auto &ss : sets) ss.destroy();
+    }
     void acquire() {
         std::unique_lock<std::mutex> g(mu);
         cv.wait(g, [&] { return holders < depth; });
@@ -312,17 +340,24 @@ void release_work(pm_batch *b) {
         for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.tasks, &w.sort_scratch})
             put(d->pool, *x);
         for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa}) put(b->ctx->pinned, *x);
-        for (auto &ev : w.e)
-            if (ev) cudaEventDestroy(ev), ev = nullptr;
-        if (w.stream) cudaStreamDestroy(w.stream), w.stream = nullptr;
-        if (w.stream2) cudaStreamSynchronize(w.stream2), cudaStreamDestroy(w.stream2), w.stream2 = nullptr;
-        if (w.stream3) cudaStreamSynchronize(w.stream3), cudaStreamDestroy(w.stream3), w.stream3 = nullptr;
-        if (w.scan_stream) cudaStreamSynchronize(w.scan_stream), cudaStreamDestroy(w.scan_stream), w.scan_stream = nullptr;
-        if (w.scan_fork) cudaEventDestroy(w.scan_fork), w.scan_fork = nullptr;
-        if (w.scan_join) cudaEventDestroy(w.scan_join), w.scan_join = nullptr;
-        for (int k = 0; k < 3; k++) {
-            if (w.fork_ev[k]) cudaEventDestroy(w.fork_ev[k]), w.fork_ev[k] = nullptr;
-            if (w.join_ev[k]) cudaEventDestroy(w.join_ev[k]), w.join_ev[k] = nullptr;
+        if (w.stream) {
+            for (cudaStream_t st : {w.stream2, w.stream3, w.scan_stream})
+                if (st) cudaStreamSynchronize(st);
+            Device::StreamSet ss;
+            ss.stream = w.stream, ss.stream2 = w.stream2, ss.stream3 = w.stream3, ss.scan_stream = w.scan_stream;
+            ss.scan_fork = w.scan_fork, ss.scan_join = w.scan_join;
+            for (int k = 0; k < 3; k++) ss.fork_ev[k] = w.fork_ev[k], ss.join_ev[k] = w.join_ev[k];
+            for (int k = 0; k < 10; k++) ss.e[k] = w.e[k];
+            w.stream = w.stream2 = w.stream3 = w.scan_stream = nullptr;
+            w.scan_fork = w.scan_join = nullptr;
+            for (int k = 0; k < 3; k++) w.fork_ev[k] = w.join_ev[k] = nullptr;
+            for (auto &ev : w.e) ev = nullptr;
+            bool keep = false;
+            if (w.locked) {   // still holding the device: the pipeline mode cannot have changed under us
+                std::lock_guard<std::mutex> g(d->mu);
+                if (d->idle_sets.size() < 16) d->idle_sets.push_back(ss), keep = true;
+            }
+            if (!keep) ss.destroy();
         }
         if (w.locked) d->release(), w.locked = false;
     }
@@ -404,43 +439,60 @@ int stage(pm_batch *b) {
         d->acquire();
         w.locked = true;
         CU(cudaSetDevice(d->id));
-        if (d->gc_scan) {
-            auto mk = [&](cudaStream_t *st, CUgreenCtx gc) {
-                CUresult r = ctx->drv.GreenCtxStreamCreate(st, gc, CU_STREAM_NON_BLOCKING, 0);
-                return r == CUDA_SUCCESS ? (int)PM_OK : fail(PM_E_CUDA, "cuGreenCtxStreamCreate failed (%d)", (int)r);
-            };
-            int rc;
-            if ((rc = mk(&w.stream, d->gc_post)) || (rc = mk(&w.stream2, d->gc_post)) || (rc = mk(&w.stream3, d->gc_post)) ||
-                (rc = mk(&w.scan_stream, d->gc_scan)))
-                return rc;
-            CU(cudaEventCreateWithFlags(&w.scan_fork, cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&w.scan_join, cudaEventDisableTiming));
-            w.sms_scan = d->sms_scan;
-            w.sms_post = d->sms_post;
-        } else if (d->depth > 1 && getenv("PM_PIPELINE_PRIORITY")) {
-            // opt-in: the short kernels of the batches that are nearly done go ahead of the next
-            // batch's scan CTAs whenever an SM frees up.  Measured on B200 (1 GiB batches, depth 5):
-            // per-batch latency 1.07 -> 0.70 ms, throughput 3.96 -> 3.70 TB/s; off by default.
-            int lo = 0, hi = 0;
-            CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-            CU(cudaStreamCreateWithPriority(&w.stream, cudaStreamNonBlocking, hi));
-            CU(cudaStreamCreateWithPriority(&w.stream2, cudaStreamNonBlocking, hi));
-            CU(cudaStreamCreateWithPriority(&w.stream3, cudaStreamNonBlocking, hi));
-            CU(cudaStreamCreateWithPriority(&w.scan_stream, cudaStreamNonBlocking, lo));
-            CU(cudaEventCreateWithFlags(&w.scan_fork, cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&w.scan_join, cudaEventDisableTiming));
-            w.sms_scan = w.sms_post = d->num_sms;
-        } else {
-            CU(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
-            CU(cudaStreamCreateWithFlags(&w.stream2, cudaStreamNonBlocking));
-            CU(cudaStreamCreateWithFlags(&w.stream3, cudaStreamNonBlocking));
-            w.sms_scan = w.sms_post = d->num_sms;
+        bool reused = false;
+        {
+            std::lock_guard<std::mutex> g(d->mu);
+            if (!d->idle_sets.empty()) {
+                Device::StreamSet ss = d->idle_sets.back();
+                d->idle_sets.pop_back();
+                w.stream = ss.stream, w.stream2 = ss.stream2, w.stream3 = ss.stream3, w.scan_stream = ss.scan_stream;
+                w.scan_fork = ss.scan_fork, w.scan_join = ss.scan_join;
+                for (int k = 0; k < 3; k++) w.fork_ev[k] = ss.fork_ev[k], w.join_ev[k] = ss.join_ev[k];
+                for (int k = 0; k < 10; k++) w.e[k] = ss.e[k];
+                reused = true;
+            }
         }
-        for (int k = 0; k < 3; k++) {
-            CU(cudaEventCreateWithFlags(&w.fork_ev[k], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&w.join_ev[k], cudaEventDisableTiming));
+        w.sms_scan = d->gc_scan ? d->sms_scan : d->num_sms;
+        w.sms_post = d->gc_scan ? d->sms_post : d->num_sms;
+        if (!reused) {
+            if (d->gc_scan) {
+                auto mk = [&](cudaStream_t *st, CUgreenCtx gc) {
+                    CUresult r = ctx->drv.GreenCtxStreamCreate(st, gc, CU_STREAM_NON_BLOCKING, 0);
+                    return r == CUDA_SUCCESS ? (int)PM_OK : fail(PM_E_CUDA, "cuGreenCtxStreamCreate failed (%d)", (int)r);
+                };
+                int rc;
+                if ((rc = mk(&w.stream, d->gc_post)) || (rc = mk(&w.stream2, d->gc_post)) || (rc = mk(&w.stream3, d->gc_post)) ||
+                    (rc = mk(&w.scan_stream, d->gc_scan)))
+                    return rc;
+                CU(cudaEventCreateWithFlags(&w.scan_fork, cudaEventDisableTiming));
+                CU(cudaEventCreateWithFlags(&w.scan_join, cudaEventDisableTiming));
+                w.sms_scan = d->sms_scan;
+                w.sms_post = d->sms_post;
+            } else if (d->depth > 1 && getenv("PM_PIPELINE_PRIORITY")) {
+                // opt-in: the short kernels of the batches that are nearly done go ahead of the next
+                // batch's scan CTAs whenever an SM frees up.  Measured on B200 (1 GiB batches, depth 5):
+                // per-batch latency 1.07 -> 0.70 ms, throughput 3.96 -> 3.70 TB/s; off by default.
+                int lo = 0, hi = 0;
+                CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+                CU(cudaStreamCreateWithPriority(&w.stream, cudaStreamNonBlocking, hi));
+                CU(cudaStreamCreateWithPriority(&w.stream2, cudaStreamNonBlocking, hi));
+                CU(cudaStreamCreateWithPriority(&w.stream3, cudaStreamNonBlocking, hi));
+                CU(cudaStreamCreateWithPriority(&w.scan_stream, cudaStreamNonBlocking, lo));
+                CU(cudaEventCreateWithFlags(&w.scan_fork, cudaEventDisableTiming));
+                CU(cudaEventCreateWithFlags(&w.scan_join, cudaEventDisableTiming));
+                w.sms_scan = w.sms_post = d->num_sms;
+            } else {
+                CU(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+                CU(cudaStreamCreateWithFlags(&w.stream2, cudaStreamNonBlocking));
+                CU(cudaStreamCreateWithFlags(&w.stream3, cudaStreamNonBlocking));
+                w.sms_scan = w.sms_post = d->num_sms;
+            }
+            for (int k = 0; k < 3; k++) {
+                CU(cudaEventCreateWithFlags(&w.fork_ev[k], cudaEventDisableTiming));
+                CU(cudaEventCreateWithFlags(&w.join_ev[k], cudaEventDisableTiming));
+            }
+            for (auto &ev : w.e) CU(cudaEventCreate(&ev));
         }
-        for (auto &ev : w.e) CU(cudaEventCreate(&ev));
         const int np = (int)w.pods.size();
         uint64_t off = kHeaderBytes;
         int rc;
@@ -967,6 +1019,7 @@ void pm_shutdown(pm_ctx *ctx) {
         cudaSetDevice(d->id);
         cudaDeviceSynchronize();
         d->pool.trim();
+        d->drop_idle_sets();
         if (d->gc_scan) ctx->drv.GreenCtxDestroy(d->gc_scan);
         if (d->gc_post) ctx->drv.GreenCtxDestroy(d->gc_post);
         delete d;
@@ -989,6 +1042,7 @@ int pm_set_pipeline(pm_ctx *ctx, int depth, int post_sms, int *scan_sms_out, int
         CU(cudaSetDevice(d->id));
         CU(cudaFree(nullptr));   // primary context up
         CU(cudaDeviceSynchronize());
+        d->drop_idle_sets();   // streams of the old mode (green-context streams must go before their context)
         if (d->gc_scan) ctx->drv.GreenCtxDestroy(d->gc_scan), d->gc_scan = nullptr;
         if (d->gc_post) ctx->drv.GreenCtxDestroy(d->gc_post), d->gc_post = nullptr;
         d->depth = depth;

@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 
+#include "../../operator_b200/csrc/pm_json.h"
 #include "../../operator_b200/csrc/pm_library.h"
 
 using namespace pm;
@@ -190,4 +191,13 @@ const char *pmt_literals(pmt_lib *l, int p) {
 extern "C" int pmt_unit_table_entries(pmt_lib *l, int p) {
     const pm::Dfa &d = l->lib.unit_dfas[pdesc(l)[p].unit];
     return d.nstates * d.stride();
+}
+
+// The streaming-ingest helpers of pm_parse: span of a top-level string member and its decoding.
+// Returns the decoded length (out holds at least n bytes), -1 when the key is absent, -2 on a bad escape.
+extern "C" long pmt_json_extract(const char *body, size_t n, const char *key, char *out) {
+    size_t b = 0, e = 0;
+    if (!pm::json_find_top_level_string(body, n, key, &b, &e)) return -1;
+    size_t len = pm::json_decode_string(body + b, e - b, out);
+    return len == (size_t)-1 ? -2 : (long)len;
 }

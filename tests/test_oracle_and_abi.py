@@ -190,3 +190,26 @@ def test_lpt_sharding_balances_bytes():
     shards = dist.shard_pods(sizes, 8)
     loads = [sum(sizes[i] for i in s) for s in shards]
     assert max(loads) - min(loads) <= max(sizes)
+
+
+def test_streaming_ingest_extracts_logs_like_a_json_parser():
+    """8(f).3: pm_parse takes "logs" out of the request without a DOM; the span finder and the
+    decoder must agree with a real JSON parser on escapes, quotes and look-alike keys."""
+    from tests.conftest import CompilerHarness
+    L = CompilerHarness().L
+    L.pmt_json_extract.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_char_p]
+    L.pmt_json_extract.restype = ctypes.c_long
+    logs = ["", "plain", "a\"b", "ends with backslash\\", "\\\"", "\\\\\"\\", "tab\tnl\nquote\" \\\" \\\\\" x", "café € \U0001F600",
+            "{\"logs\":\"decoy\"}", "x" * 70000 + "\"" + "\\" * 7 + "\"" + "y" * 9000, "\\" * 64, "\"" * 33]
+    for log in logs:
+        for doc in ({"pod": {"logs": "nested decoy", "metadata": {"name": "p\"q"}}, "logs": log, "events": ["logs", "\"logs\":\"no\""]},
+                    {"logs": log}, {"a": "\\", "b": ["\"", {"logs": "inner"}], "logs": log, "z": "\"logs\""}):
+            for ascii_only in (True, False):
+                body = json.dumps(doc, ensure_ascii=ascii_only).encode("utf-8")
+                out = ctypes.create_string_buffer(len(body) + 1)
+                n = L.pmt_json_extract(body, len(body), b"logs", out)
+                assert n >= 0 and out.raw[:n].decode("utf-8") == log, (log[:40], ascii_only, n)
+    body = json.dumps({"pod": {"logs": "only nested"}, "events": []}).encode()
+    assert L.pmt_json_extract(body, len(body), b"logs", ctypes.create_string_buffer(len(body))) == -1
+    bad = b'{"logs":"bad \\u12G4 escape"}'
+    assert L.pmt_json_extract(bad, len(bad), b"logs", ctypes.create_string_buffer(len(bad))) == -2
