@@ -154,7 +154,9 @@ int pm_batch_rescan(pm_batch *, pm_result_view *out);
 
 /* ---- newline index (a10), materialised line table of one staged pod -------------------- */
 /* Writes line_start offsets (bytes, relative to the pod) of the pod's lines into `out`
- * (host memory, capacity `cap` entries); returns the number of lines or a negative status. */
+ * (host memory, capacity `cap` entries); returns the number of lines or a negative status.  A log that was cut across
+ * devices (larger than 2 x PM_SPLIT_MIN_BYTES on a multi-GPU context) has no single table:
+ * PM_E_INVALID. */
 int64_t pm_batch_line_index(pm_batch *, int pod, int64_t *out, int64_t cap);
 
 /* ---- line table without allocation ------------------------------------------------------ */

@@ -241,6 +241,10 @@ struct PodRef {
     uint64_t tag;
     int dev = 0, local = 0;   // device slot and index among that device's pods
     uint64_t start = 0;       // offset in the device text buffer
+    // As a staged unit (pm_batch::units): which pod, which bytes of it, and how many lines of
+    // halo lie in front of / behind the lines this unit reports (0 for a pod staged whole).
+    int pod = 0, lead = 0, trail = 0;
+    uint64_t begin = 0;
 };
 
 struct DevWork {
@@ -309,6 +313,10 @@ struct pm_batch {
     pm_ctx *ctx = nullptr;
     pm_library *lib = nullptr;
     std::vector<PodRef> pods;
+    // What is actually staged: one unit per pod, or several for a log cut across devices
+    // (split_pod).  DevWork::pods and PodDev tables index units.
+    std::vector<PodRef> units;
+    std::vector<std::pair<int, int>> pod_units;   // per pod: first unit, unit count
     std::vector<DevWork> work;
     bool staged = false, submitted = false;
     // final result (pinned, batch order)
@@ -398,6 +406,65 @@ struct SoaLayout {
     }
 };
 
+// A single log larger than a device's fair share is cut at line starts into `pieces` units that
+// go to different devices.  Every unit carries a halo of H lines in front
+// of and behind the lines it reports, so that context windows, STACK runs and secondary
+// proximity windows of its own lines see exactly the text they would see in the whole log; events
+// on halo lines are dropped at gather time (they belong to the neighbour).  A trailing halo ends
+// on a non-empty line (or at the end of the pod): the line count of a unit then follows from the
+// device's count without Java's "trailing empty strings are dropped" interfering.
+void split_pod(const PodRef &p, int pod_index, int pieces, int H, std::vector<PodRef> &out) {
+    const uint8_t *s = p.ptr;
+    const size_t n = p.eff_len;
+    std::vector<size_t> cuts{0};
+    for (int k = 1; k < pieces; k++) {
+        size_t pos = n / (size_t)pieces * (size_t)k;
+        if (pos <= cuts.back()) pos = cuts.back();
+        const void *r = pos < n ? memchr(s + pos, '\n', n - pos) : nullptr;
+        if (!r) break;
+        size_t at = (size_t)((const uint8_t *)r - s) + 1;
+        if (at < n && at > cuts.back()) cuts.push_back(at);
+    }
+    cuts.push_back(p.len);
+    const int np = (int)cuts.size() - 1;
+    for (int k = 0; k < np; k++) {
+        const size_t core_begin = cuts[k], core_end = cuts[k + 1];
+        size_t begin = core_begin;
+        int lead = 0;
+        while (lead < H && begin > 0) {   // begin is a line start: step to the start of the line before
+            const void *r = begin >= 2 ? memrchr(s, '\n', begin - 1) : nullptr;
+            begin = r ? (size_t)((const uint8_t *)r - s) + 1 : 0;
+            lead++;
+        }
+        size_t end = core_end;
+        int trail = 0;
+        if (k != np - 1) {
+            while (end < n) {
+                const void *r = memchr(s + end, '\n', n - end);
+                const size_t line_end = r ? (size_t)((const uint8_t *)r - s) : n;
+                const bool empty = line_end == end || (line_end == end + 1 && s[end] == '\r');
+                trail++;
+                if (!r) {   // the pod's last line
+                    end = p.len;
+                    break;
+                }
+                end = line_end + 1;
+                if (trail >= H && !empty) break;
+            }
+            if (end >= n) end = p.len;
+        }
+        PodRef u = p;
+        u.ptr = s + begin;
+        u.len = end - begin;
+        u.eff_len = effective_len(u.ptr, u.len);
+        u.pod = pod_index;
+        u.begin = begin;
+        u.lead = lead;
+        u.trail = trail;
+        out.push_back(u);
+    }
+}
+
 int stage(pm_batch *b) {
     pm_ctx *ctx = b->ctx;
     if (b->staged) return PM_OK;
@@ -408,29 +475,50 @@ int stage(pm_batch *b) {
         b->lib->refs.fetch_add(1);
     }
     const int nd = (int)ctx->devs.size();
-    // ---- pod -> device: longest-processing-time greedy by bytes
-    std::vector<int> order(b->pods.size());
+    // ---- pods -> units: a log of more than two minimum pieces is cut across the devices
+    //      (PM_SPLIT_MIN_BYTES, default 64 MiB; PM_SPLIT_FORCE=n cuts into n pieces even on one device: tests)
+    static const size_t split_min = getenv("PM_SPLIT_MIN_BYTES") ? (size_t)strtoull(getenv("PM_SPLIT_MIN_BYTES"), nullptr, 10) : (size_t)64 << 20;
+    static const int split_force = getenv("PM_SPLIT_FORCE") ? atoi(getenv("PM_SPLIT_FORCE")) : 0;
+    b->units.clear();
+    b->pod_units.clear();
+    for (size_t i = 0; i < b->pods.size(); i++) {
+        const PodRef &p = b->pods[i];
+        const int first = (int)b->units.size();
+        int pieces = split_force > 1 ? split_force : nd;
+        if (split_min > 0) pieces = (int)std::min<size_t>((size_t)pieces, p.eff_len / split_min);
+        if (pieces > 1) {
+            const int halo = (b->lib->dev.empty() || b->lib->dev[0].ctx_slots <= 0) ? 64 : b->lib->dev[0].ctx_slots;
+            split_pod(p, (int)i, pieces, halo, b->units);
+        } else {
+            PodRef u = p;
+            u.pod = (int)i;
+            b->units.push_back(u);
+        }
+        b->pod_units.emplace_back(first, (int)b->units.size() - first);
+    }
+    // ---- unit -> device: longest-processing-time greedy by bytes
+    std::vector<int> order(b->units.size());
     for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
-    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return b->pods[x].len > b->pods[y].len; });
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return b->units[x].len > b->units[y].len; });
     std::vector<uint64_t> load(nd, 0);
     for (int i : order) {
         int best = 0;
         for (int d = 1; d < nd; d++)
             if (load[d] < load[best]) best = d;
-        b->pods[i].dev = best;
-        load[best] += b->pods[i].len + 64;
+        b->units[i].dev = best;
+        load[best] += b->units[i].len + 64;
     }
     b->work.clear();
     std::vector<int> slot_of(nd, -1);
-    for (size_t i = 0; i < b->pods.size(); i++) {
-        int d = b->pods[i].dev;
+    for (size_t i = 0; i < b->units.size(); i++) {
+        int d = b->units[i].dev;
         if (slot_of[d] < 0) {
             slot_of[d] = (int)b->work.size();
             b->work.emplace_back();
             b->work.back().slot = d;
         }
         DevWork &w = b->work[slot_of[d]];
-        b->pods[i].local = (int)w.pods.size();
+        b->units[i].local = (int)w.pods.size();
         w.pods.push_back((int)i);
     }
     // ---- per device: layout, buffers, copies
@@ -500,7 +588,7 @@ int stage(pm_batch *b) {
         PodDev *hp = w.h_pods.as<PodDev>();
         w.any_trailing_cr = 0;
         for (int k = 0; k < np; k++) {
-            PodRef &p = b->pods[w.pods[k]];
+            PodRef &p = b->units[w.pods[k]];
             p.start = off;
             hp[k].start = off;
             hp[k].eff_end = off + p.eff_len;
@@ -532,7 +620,7 @@ int stage(pm_batch *b) {
         CU(cudaMemcpyAsync(w.pods_dev.p, hp, sizeof(PodDev) * np, cudaMemcpyHostToDevice, w.stream));
         CU(cudaEventRecord(w.e[0], w.stream));
         for (int k = 0; k < np; k++) {
-            PodRef &p = b->pods[w.pods[k]];
+            PodRef &p = b->units[w.pods[k]];
             if (p.len) CU(cudaMemcpyAsync(w.text.as<uint8_t>() + p.start, p.ptr, p.len, cudaMemcpyHostToDevice, w.stream));
         }
         CU(cudaEventRecord(w.e[1], w.stream));
@@ -900,31 +988,54 @@ int finish(pm_batch *b, pm_result_view *out) {
     std::vector<int> slot_index(ctx->devs.size(), -1);
     for (size_t k = 0; k < b->work.size(); k++) slot_index[b->work[k].slot] = (int)k;
     for (size_t i = 0; i < np; i++) {
-        const PodRef &p = b->pods[i];
-        DevWork &w = b->work[slot_index[p.dev]];
-        tags[i] = p.tag;
+        tags[i] = b->pods[i].tag;
         first[i] = (int64_t)at;
-        const PodDev *hp = w.h_pods.as<PodDev>();
-        int nl = hp[p.local].n_lines;
-        if (p.len == 0) nl = 1;   // "" splits into one empty line (SPEC.md section 2)
-        nlines[i] = nl;
-        uint64_t a = dev_first[slot_index[p.dev]][p.local], e = dev_first[slot_index[p.dev]][p.local + 1];
-        if (e > a) {
-            EventOut S = SoaLayout(w.ev_cap).on(w.h_soa.p);
-            size_t cnt = e - a;
-            memcpy(R.line_start + at, S.line_start + a, cnt * 8);
-            memcpy(R.ctx_start + at, S.ctx_start + a, cnt * 8);
-            memcpy(R.ctx_end + at, S.ctx_end + a, cnt * 8);
-            memcpy(R.score + at, S.score + a, cnt * 8);
-            memcpy(R.pattern + at, S.pattern + a, cnt * 4);
-            memcpy(R.line_no + at, S.line_no + a, cnt * 4);
-            memcpy(R.line_len + at, S.line_len + a, cnt * 4);
-            memcpy(R.ctx_first + at, S.ctx_first + a, cnt * 4);
-            memcpy(R.ctx_last + at, S.ctx_last + a, cnt * 4);
-            for (size_t j = 0; j < cnt; j++) R.pod[at + j] = (int32_t)i;
-            at += cnt;
+        int64_t line_base = 0;   // lines of this pod reported by the units before the current one
+        for (int ui = b->pod_units[i].first; ui < b->pod_units[i].first + b->pod_units[i].second; ui++) {
+            const PodRef &p = b->units[ui];
+            DevWork &w = b->work[slot_index[p.dev]];
+            const PodDev *hp = w.h_pods.as<PodDev>();
+            const int core_lines = hp[p.local].n_lines - p.lead - p.trail;
+            uint64_t a = dev_first[slot_index[p.dev]][p.local], e = dev_first[slot_index[p.dev]][p.local + 1];
+            if (e > a) {
+                EventOut S = SoaLayout(w.ev_cap).on(w.h_soa.p);
+                if (b->pod_units[i].second == 1) {
+                    size_t cnt = e - a;
+                    memcpy(R.line_start + at, S.line_start + a, cnt * 8);
+                    memcpy(R.ctx_start + at, S.ctx_start + a, cnt * 8);
+                    memcpy(R.ctx_end + at, S.ctx_end + a, cnt * 8);
+                    memcpy(R.score + at, S.score + a, cnt * 8);
+                    memcpy(R.pattern + at, S.pattern + a, cnt * 4);
+                    memcpy(R.line_no + at, S.line_no + a, cnt * 4);
+                    memcpy(R.line_len + at, S.line_len + a, cnt * 4);
+                    memcpy(R.ctx_first + at, S.ctx_first + a, cnt * 4);
+                    memcpy(R.ctx_last + at, S.ctx_last + a, cnt * 4);
+                    for (size_t j = 0; j < cnt; j++) R.pod[at + j] = (int32_t)i;
+                    at += cnt;
+                } else {   // a piece of a split log: own lines only, renumbered and re-based to the pod
+                    const int64_t shift = line_base - p.lead;
+                    for (uint64_t j = a; j < e; j++) {
+                        const int ln = S.line_no[j];
+                        if (ln <= p.lead || ln > p.lead + core_lines) continue;
+                        R.line_start[at] = S.line_start[j] + (int64_t)p.begin;
+                        R.ctx_start[at] = S.ctx_start[j] + (int64_t)p.begin;
+                        R.ctx_end[at] = S.ctx_end[j] + (int64_t)p.begin;
+                        R.score[at] = S.score[j];
+                        R.pattern[at] = S.pattern[j];
+                        R.line_no[at] = (int32_t)(ln + shift);
+                        R.line_len[at] = S.line_len[j];
+                        R.ctx_first[at] = (int32_t)(S.ctx_first[j] + shift);
+                        R.ctx_last[at] = (int32_t)(S.ctx_last[j] + shift);
+                        R.pod[at] = (int32_t)i;
+                        at++;
+                    }
+                }
+            }
+            line_base += core_lines;
         }
+        nlines[i] = b->pods[i].len == 0 ? 1 : (int32_t)line_base;   // "" splits into one empty line (SPEC.md section 2)
     }
+    total_events = at;
     first[np] = (int64_t)at;
     pm_result_view &v = b->view;
     memset(&v, 0, sizeof v);
@@ -1249,7 +1360,9 @@ void pm_batch_release(pm_batch *b) {
 
 int64_t pm_batch_line_index(pm_batch *b, int pod, int64_t *out, int64_t cap) {
     if (!b || pod < 0 || pod >= (int)b->pods.size()) return fail(PM_E_INVALID, "bad pod index");
-    const PodRef &p = b->pods[pod];
+    if (!b->staged || b->pod_units[pod].second != 1)
+        return fail(PM_E_INVALID, b->staged ? "the log was cut across devices: no single line table" : "batch is not staged");
+    const PodRef &p = b->units[b->pod_units[pod].first];
     DevWork *w = nullptr;
     for (auto &x : b->work)
         if (x.slot == p.dev) w = &x;

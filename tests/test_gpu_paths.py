@@ -154,3 +154,50 @@ def test_batches_in_flight_share_a_device(tmp_path):
     script.write_text(_PIPE % ROOT)
     r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "pipeline ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+_SPLIT = r"""
+import sys
+sys.path.insert(0, %r)
+import numpy as np
+from operator_b200 import Engine, synth
+from oracle import oracle
+lib_json, wit, swit = synth.make_library(50)
+olib = oracle.load_library(lib_json)
+big, _ = synth.make_corpus(900000, wit, swit, p_hit=3e-2, seed=31)
+crlf, _ = synth.make_corpus(400000, wit, swit, p_hit=3e-2, seed=32, crlf=True)
+gaps = bytes(big[:300000]).replace(b"\n", b"\n\n\n", 400) + b"\n\n\n\n"      # runs of empty lines around the cuts, empty tail
+small = bytes(big[:15000])
+logs = [bytes(big), bytes(crlf), gaps, small, b"", bytes(big[:200000]) + b"no newline at the end " + wit[0].encode()]
+eng = Engine(0)
+eng.compile_library(lib_json).publish()
+res = eng.scan(logs)
+n_split = 0
+for pod, log in enumerate(logs):
+    want = [(e.line_no, e.pattern, e.ctx_first, e.ctx_last, e.ctx_start, e.ctx_end, e.score) for e in oracle.analyze(log, olib)]
+    got = [(g["line_no"], g["pattern"], g["ctx_first"], g["ctx_last"], g["ctx_start"], g["ctx_end"], g["score"]) for g in res.events_of(pod)]
+    assert got == want, (pod, len(got), len(want), [x for x in zip(got, want) if x[0] != x[1]][:3])
+    assert int(res.pod_n_lines[pod]) == len(oracle.split_lines(log)), (pod, int(res.pod_n_lines[pod]))
+assert res.n_events > 300 and res.n_events == sum(len(res.events_of(k)) for k in range(len(logs)))
+b = eng.batch(); b.add_pod(logs[0], 0); b.add_pod(small, 1); b.stage(); b.rescan()
+try:
+    b.line_index(0, 10)
+    raise SystemExit("line_index of a split log must fail")
+except Exception as e:
+    assert "cut across" in str(e), e
+assert len(b.line_index(1, int(res.pod_n_lines[3]))) == int(res.pod_n_lines[3])
+b.release()
+eng.close()
+print("split ok")
+"""
+
+
+def test_one_large_log_is_cut_across_devices(tmp_path):
+    """8(e): a log above the split threshold is cut at line starts into units with context halos
+    (here forced onto however many GPUs there are, 3 pieces at least); events, line numbers, byte
+    offsets, contexts and scores equal the oracle's on the whole log."""
+    script = tmp_path / "split.py"
+    script.write_text(_SPLIT % ROOT)
+    env = dict(os.environ, PM_SPLIT_FORCE="3", PM_SPLIT_MIN_BYTES="60000")
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "split ok" in r.stdout, r.stdout[-1500:] + r.stderr[-2500:]
