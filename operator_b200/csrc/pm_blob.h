@@ -5,7 +5,7 @@
 //   bitmap      gram filter, 2^filter_log2_bits bits, staged into shared memory by k_scan
 //   gram_keys   open-addressing table gram -> probe run (exact check of a filter hit)
 //   probes      (pattern, literal, offset of the gram inside the literal)
-//   litpool     literal bytes followed by their case masks
+//   litpool     literal bytes followed by their case masks (both padded to whole 32-bit words with 0xFF)
 //   units       one verify-DFA descriptor per regex unit (primaries, secondaries, STACK)
 //   classmaps   256-byte byte->class maps
 //   tables      u16 next-state tables
@@ -24,7 +24,7 @@
 namespace pm {
 
 constexpr uint32_t kBlobMagic = 0x424C4D50u;   // "PMLB"
-constexpr uint32_t kBlobVersion = 7;
+constexpr uint32_t kBlobVersion = 8;
 constexpr int kGramLen = 4;        // bytes per gram = one aligned 32-bit text word
 constexpr int kMinLiteral = 7;     // any 7-byte window covers one aligned 4-byte word
 constexpr uint32_t kGramEmpty = 0xFFFFFFFFu;   // 0xFF never occurs in valid UTF-8
@@ -47,7 +47,7 @@ struct BlobHeader {
 
 struct Probe {
     uint32_t pattern;
-    uint32_t lit_off;    // into litpool: bytes[lit_len] then mask[lit_len]
+    uint32_t lit_off;    // into litpool, 4-byte aligned: bytes[lit_len], 0xFF to a whole word, mask[lit_len], 0xFF to a whole word
     uint16_t lit_len;
     uint16_t gram_off;   // offset of this gram inside the literal
 };

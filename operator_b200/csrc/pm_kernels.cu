@@ -485,14 +485,22 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
                 if (q < qn) {
                     pr = probes[q0 + q];
                     if (p >= kHeaderBytes + pr.gram_off && p - pr.gram_off + pr.lit_len <= total) {
+                        // word-wise: literal and case mask are 4-byte aligned and 0xFF-padded (pm_library.cc),
+                        // the text word at an arbitrary offset comes from two aligned words and a funnel shift
                         const unsigned long long st = p - pr.gram_off;
-                        const uint8_t *lit = litpool + pr.lit_off, *msk = lit + pr.lit_len;
+                        const uint32_t n_words = (pr.lit_len + 3u) >> 2, sh = (uint32_t)(st & 3) * 8;
+                        const uint32_t *lit = reinterpret_cast<const uint32_t *>(litpool + pr.lit_off), *msk = lit + n_words;
+                        const uint32_t *tw = reinterpret_cast<const uint32_t *>(text + (st & ~3ull));
+                        uint32_t lo = tw[0];
                         eq = true;
-                        for (uint32_t j = 0; j < pr.lit_len; j++)
-                            if ((uint8_t)(text[st + j] | msk[j]) != lit[j]) {
+                        for (uint32_t j = 0; j < n_words; j++) {
+                            const uint32_t hi = tw[j + 1];
+                            if ((__funnelshift_r(lo, hi, sh) | msk[j]) != lit[j]) {
                                 eq = false;
                                 break;
                             }
+                            lo = hi;
+                        }
                     }
                 }
                 if (eq) {

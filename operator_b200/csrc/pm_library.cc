@@ -223,9 +223,14 @@ void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mo
     out.fold = fold;
     std::map<uint32_t, std::vector<Probe>> by_gram;
     for (auto &c : chosen) {
+        // 4-byte aligned, both halves padded to whole words with 0xFF: k_confirm compares word-wise and
+        // (text | 0xFF) == 0xFF holds for whatever follows the literal in the text
+        while (out.litpool.size() % 4) out.litpool.push_back(0xFF);
         uint32_t lit_off = (uint32_t)out.litpool.size();
         out.litpool.insert(out.litpool.end(), c.lit->bytes.begin(), c.lit->bytes.end());
+        while (out.litpool.size() % 4) out.litpool.push_back(0xFF);
         out.litpool.insert(out.litpool.end(), c.lit->mask.begin(), c.lit->mask.end());
+        while (out.litpool.size() % 4) out.litpool.push_back(0xFF);
         for (int k = 0; k < 4; k++) {
             Probe pr;
             pr.pattern = (uint32_t)c.pattern;

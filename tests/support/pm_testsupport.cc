@@ -151,7 +151,7 @@ int pmt_filter_triggers(pmt_lib *l, int p, const uint8_t *text, size_t n, int ph
             if (i < pr[k].gram_off) continue;
             size_t st = i - pr[k].gram_off;
             if (st + pr[k].lit_len > n) continue;
-            const uint8_t *lit = lp + pr[k].lit_off, *m = lit + pr[k].lit_len;
+            const uint8_t *lit = lp + pr[k].lit_off, *m = lit + ((pr[k].lit_len + 3u) & ~3u);
             bool eq = true;
             for (size_t j = 0; j < pr[k].lit_len && eq; j++) eq = ((text[st + j] | m[j]) == lit[j]);
             if (eq) return 1;
