@@ -1060,7 +1060,7 @@ __global__ void __launch_bounds__(kSortChunk / 2) k_sort_chunks(const unsigned l
     for (unsigned i = threadIdx.x; i < kSortChunk; i += blockDim.x) chunks[base + i] = keys[i];
 }
 
-__global__ void __launch_bounds__(256) k_sort_merge(const unsigned long long *__restrict__ chunks, const ScanCounters *ctr, unsigned long long raw_cap,
+__global__ void __launch_bounds__(1024) k_sort_merge(const unsigned long long *__restrict__ chunks, const ScanCounters *ctr, unsigned long long raw_cap,
                                                     unsigned long long *__restrict__ sorted) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned long long *sk = reinterpret_cast<unsigned long long *>(smem_raw);   // all sorted chunks (<= 128 KiB)
@@ -1420,7 +1420,7 @@ __global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ 
 // One thread per key.  The row of a key goes to out[rank], rank = position of the key in the
 // sorted, de-duplicated uniq[]; so keys[] can be the raw queue, planned and checked while the sort
 // was still running on another stream (duplicates write identical rows).
-__global__ void __launch_bounds__(128) k_finalize(const uint8_t *__restrict__ blob, BlobHeader h, const unsigned long long *__restrict__ keys,
+__global__ void __launch_bounds__(512) k_finalize(const uint8_t *__restrict__ blob, BlobHeader h, const unsigned long long *__restrict__ keys,
                                                   const unsigned long long *n_keys_ptr, const unsigned long long *__restrict__ uniq,
                                                   const unsigned long long *n_unique_ptr, unsigned long long ev_cap, EventOut out,
                                                   const Item *__restrict__ items, const unsigned char *__restrict__ results,
@@ -1682,9 +1682,11 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
     if (fork) cudaStreamWaitEvent(s, join_ev, 0);
     if (uniq_ready) cudaStreamWaitEvent(s, uniq_ready, 0);   // the sort ran beside plan/check
-    unsigned fb = (unsigned)((key_cap + 127) / 128);
-    if (fb > (unsigned)num_sms * 8u) fb = (unsigned)num_sms * 8u;
-    k_finalize<<<fb, 128, 0, s>>>(lib.blob, lib.h, keys, n_keys_dev, uniq, n_unique_dev, ev_cap, out, items, rs.results,
+    // few, full CTAs: with several batches in flight every SM a small kernel sits on is an SM the next
+    // batch's scan CTA (a whole SM each) has to wait for
+    unsigned fb = (unsigned)((key_cap + 511) / 512);
+    if (fb > (unsigned)num_sms * 2u) fb = (unsigned)num_sms * 2u;
+    k_finalize<<<fb, 512, 0, s>>>(lib.blob, lib.h, keys, n_keys_dev, uniq, n_unique_dev, ev_cap, out, items, rs.results,
                                   reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);
     return cudaGetLastError();
 }
@@ -1695,7 +1697,7 @@ cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters 
     k_sort_chunks<<<kSortChunks, kSortChunk / 2, 0, s>>>(raw, ctr, raw_cap, chunks);
     cudaError_t e = cudaFuncSetAttribute(k_sort_merge, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSort * 8);
     if (e != cudaSuccess) return e;
-    k_sort_merge<<<kSmallSort / 256, 256, kSmallSort * 8, s>>>(chunks, ctr, raw_cap, sorted);
+    k_sort_merge<<<kSmallSort / 1024, 1024, kSmallSort * 8, s>>>(chunks, ctr, raw_cap, sorted);
     k_sort_unique<<<1, 1024, 0, s>>>(sorted, ctr, raw_cap, uniq, n_unique, big_flag);
     return cudaGetLastError();
 }
