@@ -555,12 +555,12 @@ __device__ __forceinline__ uint32_t warp_walk_line(const uint8_t *__restrict__ t
         uint32_t k = p0;
         for (; k + 4 <= p1 && s0 != acc && s0 != dead; k += 4) {
             const uint32_t c0 = cls[k], c1 = cls[k + 1], c2 = cls[k + 2], c3 = cls[k + 3];
-            s0 = __ldg(tab + s0 * stride + c0);
-            s0 = __ldg(tab + s0 * stride + c1);
-            s0 = __ldg(tab + s0 * stride + c2);
-            s0 = __ldg(tab + s0 * stride + c3);
+            s0 = __ldg(tab + (s0 * stride + c0));
+            s0 = __ldg(tab + (s0 * stride + c1));
+            s0 = __ldg(tab + (s0 * stride + c2));
+            s0 = __ldg(tab + (s0 * stride + c3));
         }
-        for (; k < p1 && s0 != acc && s0 != dead; k++) s0 = __ldg(tab + s0 * stride + cls[k]);
+        for (; k < p1 && s0 != acc && s0 != dead; k++) s0 = __ldg(tab + (s0 * stride + cls[k]));
         return s0;
     };
     bool have_cmap = false;
@@ -641,6 +641,9 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
         if (lane >= 16 || p16 >= 16ull * (lane + 1)) around = *reinterpret_cast<const uint4 *>(text + a);
         const UnitDesc ud = reinterpret_cast<const UnitDesc *>(blob + h.off_units)[pd[pat].unit];
         const uint16_t *gtab = reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off;
+        // (opaque to the compiler from here on: otherwise it re-derives the pointer from the uniform base
+        // and the 32-bit table offset inside every lookup, a 64-bit carry chain of five instructions)
+        asm volatile("" : "+l"(gtab));
         warp_touch_table(gtab, (uint32_t)ud.nstates * ud.stride * 2u);
         uint32_t m = newline_mask16(around);
         if (lane == 16) m &= ~((1u << (p - p16)) - 1u);          // forward search starts at p
@@ -689,7 +692,7 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
         const uint32_t stride = ud.stride, acc = ud.accept_state;
         uint32_t st = warp_walk_line(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, blob + h.off_classmaps + ud.classmap_off,
                                      s_cmap[warp], s_cls[warp]);
-        if (st != acc) st = __ldg(gtab + st * stride + stride - 1);
+        if (st != acc) st = __ldg(gtab + (st * stride + stride - 1));
         if (lane == 0) {
             if (st == acc) {
                 unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
