@@ -10,7 +10,7 @@ CXXFLAGS := -O2 -std=c++17 -fPIC -Wall -Wno-unused-function -Iinclude -I/usr/loc
 NVFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Iinclude -Xptxas -v --fmad=false
 
 CSRC := operator_b200/csrc
-HOST_SRCS := $(CSRC)/pm_json.cc $(CSRC)/pm_regex.cc $(CSRC)/pm_automata.cc $(CSRC)/pm_literal.cc $(CSRC)/pm_library.cc $(CSRC)/pm_service.cc
+HOST_SRCS := $(CSRC)/pm_json.cc $(CSRC)/pm_regex.cc $(CSRC)/pm_automata.cc $(CSRC)/pm_literal.cc $(CSRC)/pm_library.cc $(CSRC)/pm_split.cc $(CSRC)/pm_service.cc
 HOST_OBJS := $(HOST_SRCS:.cc=.o)
 CU_SRCS := $(wildcard $(CSRC)/*.cu)
 CU_OBJS := $(CU_SRCS:.cu=.o)

@@ -23,6 +23,7 @@
 
 #include "pm_kernels.h"
 #include "pm_library.h"
+#include "pm_split.h"
 #include "podmortem_scan.h"
 
 using namespace pm;
@@ -298,15 +299,6 @@ bool tiny_queues() {
     return v;
 }
 
-// Length without trailing "\r?\n" separators (Java split drops trailing empty strings).
-size_t effective_len(const uint8_t *p, size_t n) {
-    while (n > 0 && p[n - 1] == '\n') {
-        n--;
-        if (n > 0 && p[n - 1] == '\r') n--;
-    }
-    return n;
-}
-
 }  // namespace
 
 struct pm_batch {
@@ -406,65 +398,6 @@ struct SoaLayout {
     }
 };
 
-// A single log larger than a device's fair share is cut at line starts into `pieces` units that
-// go to different devices.  Every unit carries a halo of H lines in front
-// of and behind the lines it reports, so that context windows, STACK runs and secondary
-// proximity windows of its own lines see exactly the text they would see in the whole log; events
-// on halo lines are dropped at gather time (they belong to the neighbour).  A trailing halo ends
-// on a non-empty line (or at the end of the pod): the line count of a unit then follows from the
-// device's count without Java's "trailing empty strings are dropped" interfering.
-void split_pod(const PodRef &p, int pod_index, int pieces, int H, std::vector<PodRef> &out) {
-    const uint8_t *s = p.ptr;
-    const size_t n = p.eff_len;
-    std::vector<size_t> cuts{0};
-    for (int k = 1; k < pieces; k++) {
-        size_t pos = n / (size_t)pieces * (size_t)k;
-        if (pos <= cuts.back()) pos = cuts.back();
-        const void *r = pos < n ? memchr(s + pos, '\n', n - pos) : nullptr;
-        if (!r) break;
-        size_t at = (size_t)((const uint8_t *)r - s) + 1;
-        if (at < n && at > cuts.back()) cuts.push_back(at);
-    }
-    cuts.push_back(p.len);
-    const int np = (int)cuts.size() - 1;
-    for (int k = 0; k < np; k++) {
-        const size_t core_begin = cuts[k], core_end = cuts[k + 1];
-        size_t begin = core_begin;
-        int lead = 0;
-        while (lead < H && begin > 0) {   // begin is a line start: step to the start of the line before
-            const void *r = begin >= 2 ? memrchr(s, '\n', begin - 1) : nullptr;
-            begin = r ? (size_t)((const uint8_t *)r - s) + 1 : 0;
-            lead++;
-        }
-        size_t end = core_end;
-        int trail = 0;
-        if (k != np - 1) {
-            while (end < n) {
-                const void *r = memchr(s + end, '\n', n - end);
-                const size_t line_end = r ? (size_t)((const uint8_t *)r - s) : n;
-                const bool empty = line_end == end || (line_end == end + 1 && s[end] == '\r');
-                trail++;
-                if (!r) {   // the pod's last line
-                    end = p.len;
-                    break;
-                }
-                end = line_end + 1;
-                if (trail >= H && !empty) break;
-            }
-            if (end >= n) end = p.len;
-        }
-        PodRef u = p;
-        u.ptr = s + begin;
-        u.len = end - begin;
-        u.eff_len = effective_len(u.ptr, u.len);
-        u.pod = pod_index;
-        u.begin = begin;
-        u.lead = lead;
-        u.trail = trail;
-        out.push_back(u);
-    }
-}
-
 int stage(pm_batch *b) {
     pm_ctx *ctx = b->ctx;
     if (b->staged) return PM_OK;
@@ -488,7 +421,19 @@ int stage(pm_batch *b) {
         if (split_min > 0) pieces = (int)std::min<size_t>((size_t)pieces, p.eff_len / split_min);
         if (pieces > 1) {
             const int halo = (b->lib->dev.empty() || b->lib->dev[0].ctx_slots <= 0) ? 64 : b->lib->dev[0].ctx_slots;
-            split_pod(p, (int)i, pieces, halo, b->units);
+            std::vector<SplitUnit> cut;   // pm_split.cc
+            split_log(p.ptr, p.len, pieces, halo, cut);
+            for (const SplitUnit &c : cut) {
+                PodRef u = p;
+                u.ptr = p.ptr + c.begin;
+                u.len = c.end - c.begin;
+                u.eff_len = effective_len(u.ptr, u.len);
+                u.pod = (int)i;
+                u.begin = c.begin;
+                u.lead = c.lead;
+                u.trail = c.trail;
+                b->units.push_back(u);
+            }
         } else {
             PodRef u = p;
             u.pod = (int)i;

@@ -11,6 +11,7 @@
 
 #include "../../operator_b200/csrc/pm_json.h"
 #include "../../operator_b200/csrc/pm_library.h"
+#include "../../operator_b200/csrc/pm_split.h"
 
 using namespace pm;
 
@@ -200,4 +201,17 @@ extern "C" long pmt_json_extract(const char *body, size_t n, const char *key, ch
     if (!pm::json_find_top_level_string(body, n, key, &b, &e)) return -1;
     size_t len = pm::json_decode_string(body + b, e - b, out);
     return len == (size_t)-1 ? -2 : (long)len;
+}
+
+// split_log (pm_split.cc): writes begin, end, lead, trail per unit into out[4*k ..]; returns the unit count.
+extern "C" int pmt_split(const uint8_t *log, size_t n, int pieces, int halo, int64_t *out, int cap) {
+    std::vector<pm::SplitUnit> u;
+    pm::split_log(log, n, pieces, halo, u);
+    for (size_t k = 0; k < u.size() && (int)k < cap; k++) {
+        out[4 * k] = (int64_t)u[k].begin;
+        out[4 * k + 1] = (int64_t)u[k].end;
+        out[4 * k + 2] = u[k].lead;
+        out[4 * k + 3] = u[k].trail;
+    }
+    return (int)u.size();
 }

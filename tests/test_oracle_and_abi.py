@@ -213,3 +213,47 @@ def test_streaming_ingest_extracts_logs_like_a_json_parser():
     assert L.pmt_json_extract(body, len(body), b"logs", ctypes.create_string_buffer(len(body))) == -1
     bad = b'{"logs":"bad \\u12G4 escape"}'
     assert L.pmt_json_extract(bad, len(bad), b"logs", ctypes.create_string_buffer(len(bad))) == -2
+
+
+def test_split_log_units_add_up():
+    """8(e): a log cut into units with halos.  The lines a unit reports (its line count under the
+    Java split model minus its halos) must tile the log's lines exactly, whatever the cut points
+    land on: runs of empty lines, CRLF, no final newline, fewer lines than pieces."""
+    import random
+    from tests.conftest import CompilerHarness
+    L = CompilerHarness().L
+    L.pmt_split.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
+    rnd = random.Random(5)
+
+    def nlines(b):
+        return len(oracle.split_lines(b)) if b else 0
+
+    for trial in range(300):
+        sep = b"\r\n" if trial % 3 == 0 else b"\n"
+        n = rnd.choice([1, 2, 3, 7, 40, 300])
+        lines = [b"" if rnd.random() < 0.35 else bytes(rnd.choice(b"abc xyz\r") for _ in range(rnd.randint(1, 30))).rstrip(b"\r") for _ in range(n)]
+        log = sep.join(lines) + rnd.choice([b"", sep, sep * 3])
+        pieces, halo = rnd.randint(2, 6), rnd.randint(0, 5)
+        out = (ctypes.c_int64 * (4 * 16))()
+        k = L.pmt_split(log, len(log), pieces, halo, out, 16)
+        assert 1 <= k <= pieces
+        units = [tuple(out[4 * i:4 * i + 4]) for i in range(k)]
+        total, reported = nlines(log), 0
+        prev_core_end = 0
+        for i, (b, e, lead, trail) in enumerate(units):
+            assert 0 <= b <= e <= len(log) and (b == 0 or log[b - 1:b] == b"\n")
+            text = log[b:e]
+            core = nlines(text) - lead - trail
+            assert core >= 0 and lead <= halo, (trial, units)
+            assert lead == halo or b == 0                        # a full halo unless the log starts first
+            if i < k - 1:
+                assert trail >= halo or e == len(log)
+            # the first reported line starts where the previous unit's reported lines ended
+            starts = [s for s, _ in oracle.split_lines(text)] if text else []
+            if core > 0:
+                assert b + starts[lead] == prev_core_end, (trial, i, units)
+                last = lead + core - 1
+                nxt = b + starts[last + 1] if last + 1 < len(starts) else None
+                prev_core_end = nxt if nxt is not None else len(log)
+            reported += core
+        assert reported == total, (trial, total, reported, units, log)
