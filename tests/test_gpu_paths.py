@@ -154,6 +154,9 @@ def test_batches_in_flight_share_a_device(tmp_path):
     script.write_text(_PIPE % ROOT)
     r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "pipeline ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+    # the same with every queue starting tiny: overflow -> grow -> rerun while other batches are in flight
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600, env=dict(os.environ, PM_TEST_TINY_QUEUES="1"))
+    assert r.returncode == 0 and "pipeline ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
 
 
 _SPLIT = r"""
