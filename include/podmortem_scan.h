@@ -128,6 +128,13 @@ int pm_set_pipeline(pm_ctx *, int depth, int post_sms, int *scan_sms, int *post_
 int pm_library_compile(pm_ctx *, const uint8_t *spec, size_t n, pm_library **out, pm_compile_report *rep);
 /* Replicates the tables to every device of the context and makes the library current. */
 int pm_library_publish(pm_ctx *, pm_library *);
+/* A compiled library as bytes and back (the sync step,
+ * PatternSyncService.java:228-253, compiles once and leaves the result beside the YAML; the /parse
+ * service loads it instead of compiling again).  The bytes belong to the library and live as long
+ * as it does.  pm_library_load rejects bytes of another compiler version (PM_E_UNSUPPORTED) and
+ * damaged ones (PM_E_INVALID); a loaded library is published like a compiled one. */
+int pm_library_serialize(pm_library *, const uint8_t **bytes, size_t *n);
+int pm_library_load(pm_ctx *, const uint8_t *bytes, size_t n, pm_library **out);
 void pm_library_free(pm_library *);
 int pm_library_pattern_count(const pm_library *);
 /* JSON text with per-pattern id/name/severity/category, for marshalling AnalysisResult. */

@@ -66,4 +66,8 @@ struct CompiledLibrary {
 // Returns PM_OK or a negative pm_status; `rep` always describes the outcome.
 int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile_report &rep);
 
+// Compiled library <-> bytes (what the sync hook leaves beside the YAML; pm_library.cc).
+void serialize_library(const CompiledLibrary &lib, std::vector<uint8_t> &out);
+int deserialize_library(const uint8_t *data, size_t n, CompiledLibrary &lib, std::string &err);
+
 }  // namespace pm

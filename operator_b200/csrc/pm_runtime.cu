@@ -201,6 +201,7 @@ struct pm_library {
     std::vector<void *> dev_blobs;
     std::vector<AdaptState> adapt;
     std::mutex adapt_mu;              // guards dev[].fv against a concurrent maybe_adapt
+    std::vector<uint8_t> saved;       // pm_library_serialize
     pm_ctx *owner = nullptr;
     uint64_t generation = 0;   // unique per compiled library (result-cache key of pm_parse)
 };
@@ -1154,6 +1155,32 @@ int pm_library_compile(pm_ctx *ctx, const uint8_t *spec, size_t n, pm_library **
     if (l->lib.patterns.size() >= (1u << kPatternBits)) {
         delete l;
         return fail(PM_E_TOO_COMPLEX, "more than %u patterns", 1u << kPatternBits);
+    }
+    *out = l;
+    return PM_OK;
+}
+
+int pm_library_serialize(pm_library *l, const uint8_t **bytes, size_t *n) {
+    if (!l || !bytes || !n) return fail(PM_E_INVALID, "null argument");
+    if (l->saved.empty()) serialize_library(l->lib, l->saved);
+    *bytes = l->saved.data();
+    *n = l->saved.size();
+    return PM_OK;
+}
+
+int pm_library_load(pm_ctx *ctx, const uint8_t *bytes, size_t n, pm_library **out) {
+    if (!out || !bytes) return fail(PM_E_INVALID, "null argument");
+    *out = nullptr;
+    static std::atomic<uint64_t> next_generation{1ull << 32};
+    pm_library *l = new pm_library();
+    l->owner = ctx;
+    l->generation = next_generation.fetch_add(1);
+    std::string err;
+    int rc = deserialize_library(bytes, n, l->lib, err);
+    if (rc == PM_OK && l->lib.patterns.size() >= (1u << kPatternBits)) rc = PM_E_TOO_COMPLEX, err = "too many patterns";
+    if (rc != PM_OK) {
+        delete l;
+        return fail(rc, "%s", err.c_str());
     }
     *out = l;
     return PM_OK;

@@ -69,7 +69,7 @@ ABI_SYMBOLS = ["pm_abi_version", "pm_init", "pm_init_devices", "pm_shutdown", "p
                "pm_library_publish", "pm_library_free", "pm_library_pattern_count", "pm_library_pattern_meta_json",
                "pm_host_alloc", "pm_host_free", "pm_batch_begin", "pm_batch_add_pod", "pm_batch_submit", "pm_batch_wait",
                "pm_batch_release", "pm_batch_stage", "pm_batch_rescan", "pm_batch_line_index", "pm_parse",
-               "pm_line_index_noalloc", "pm_noalloc_last_error", "pm_set_pipeline", "pm_parse_stats"]
+               "pm_line_index_noalloc", "pm_noalloc_last_error", "pm_set_pipeline", "pm_parse_stats", "pm_library_serialize", "pm_library_load"]
 
 
 def load_library() -> ctypes.CDLL:
@@ -91,6 +91,8 @@ def load_library() -> ctypes.CDLL:
     d.pm_device_count.argtypes = [vp]
     d.pm_library_compile.argtypes = [vp, ctypes.c_char_p, sz, _P(vp), _P(CompileReport)]
     d.pm_library_publish.argtypes = [vp, vp]
+    d.pm_library_serialize.argtypes = [vp, _P(vp), _P(sz)]
+    d.pm_library_load.argtypes = [vp, ctypes.c_char_p, sz, _P(vp)]
     d.pm_library_free.argtypes = [vp]
     d.pm_library_free.restype = None
     d.pm_library_pattern_count.argtypes = [vp]
@@ -178,6 +180,12 @@ class Library:
     def publish(self) -> "Library":
         _check(load_library().pm_library_publish(self._engine._ctx, self._h))
         return self
+
+    def to_bytes(self) -> bytes:
+        """The compiled library as bytes (pm_library_serialize): what the sync hook leaves beside the YAML."""
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        _check(load_library().pm_library_serialize(self._h, ctypes.byref(p), ctypes.byref(n)))
+        return ctypes.string_at(p, n.value)
 
     def free(self):
         if self._h:
@@ -289,6 +297,14 @@ class Engine:
         if rc != PM_OK:
             raise ScanError(rc, rep.message.decode("utf-8", "replace"), rep.as_dict())
         return Library(self, h, rep)
+
+    def load_library(self, data: bytes) -> Library:
+        """A library compiled earlier (Library.to_bytes) without compiling again (pm_library_load)."""
+        h = ctypes.c_void_p()
+        _check(load_library().pm_library_load(self._ctx, data, len(data), ctypes.byref(h)))
+        lib = Library(self, h, CompileReport())
+        lib.report["n_patterns"] = lib.n_patterns
+        return lib
 
     def batch(self) -> Batch:
         return Batch(self)

@@ -17,7 +17,7 @@ names file, pattern id and regex offset) instead of logging a count.
 from __future__ import annotations
 
 import os
-from typing import Dict, List, Tuple
+from typing import Dict, List, Optional, Tuple
 
 import yaml
 
@@ -76,9 +76,44 @@ def load_pattern_files(paths: List[str]) -> Tuple[List[dict], List[Tuple[int, st
     return libs, index
 
 
-def validate_patterns(engine: Engine, repo_path: str, publish: bool = True) -> Library:
+COMPILED_NAME = ".podmortem-compiled.pmlb"   # beside the YAML tree; not a .yaml, so the file count of the reference is unchanged
+
+
+def _fingerprint(paths: List[str]) -> bytes:
+    """SHA-256 over the pattern files (relative order, names and contents): a compiled library on the
+    volume is only good for exactly the YAML it was compiled from."""
+    import hashlib
+    h = hashlib.sha256()
+    for path in paths:
+        with open(path, "rb") as f:
+            data = f.read()
+        h.update(os.path.basename(path).encode() + b"\0" + str(len(data)).encode() + b"\0" + data)
+    return h.digest()
+
+
+def load_compiled(engine: Engine, repo_path: str, publish: bool = True) -> Optional[Library]:
+    """Service start-up: take the library the sync step compiled (8(f).2) if it matches the YAML on the
+    volume; None when there is none, it is stale, or it was built by another compiler version."""
+    path = os.path.join(repo_path, COMPILED_NAME)
+    if not os.path.isfile(path):
+        return None
+    with open(path, "rb") as f:
+        data = f.read()
+    if len(data) < 32 or data[:32] != _fingerprint(discover_pattern_files(repo_path)):
+        return None
+    try:
+        lib = engine.load_library(data[32:])
+    except ScanError:
+        return None
+    if publish:
+        lib.publish()
+    return lib
+
+
+def validate_patterns(engine: Engine, repo_path: str, publish: bool = True, save: bool = False) -> Library:
     """Sync-time hook (replaces the count in PatternSyncService.validatePatterns, :228-253):
-    compile everything under repo_path; on rejection raise with file + pattern id + offset."""
+    compile everything under repo_path; on rejection raise with file + pattern id + offset.
+    save: leave the compiled library beside the YAML for the service to load (load_compiled)."""
     paths = discover_pattern_files(repo_path)
     libs, index = load_pattern_files(paths)
     try:
@@ -95,6 +130,11 @@ def validate_patterns(engine: Engine, repo_path: str, publish: bool = True) -> L
         if rep.get("regex_offset", -1) >= 0:
             where += " at regex offset %d" % rep["regex_offset"]
         raise PatternCompileError("%s: %s" % (where, e.message), rep, src) from None
+    if save:
+        tmp = os.path.join(repo_path, COMPILED_NAME + ".tmp")
+        with open(tmp, "wb") as f:
+            f.write(_fingerprint(paths) + lib.to_bytes())
+        os.replace(tmp, os.path.join(repo_path, COMPILED_NAME))
     if publish:
         lib.publish()
     return lib

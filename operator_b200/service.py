@@ -48,7 +48,9 @@ def main():
     ap.add_argument("--port", type=int, default=8080)
     args = ap.parse_args()
     engine = Engine()
-    patterns.validate_patterns(engine, args.patterns)
+    # the library the operator's sync step compiled, if it is there and current; else compile now and leave it
+    if patterns.load_compiled(engine, args.patterns) is None:
+        patterns.validate_patterns(engine, args.patterns, save=True)
     ThreadingHTTPServer(("0.0.0.0", args.port), make_handler(engine)).serve_forever()
 
 

@@ -215,3 +215,33 @@ extern "C" int pmt_split(const uint8_t *log, size_t n, int pieces, int halo, int
     }
     return (int)u.size();
 }
+
+// serialize_library / deserialize_library (pm_library.cc).  pmt_saved: the bytes of a compiled library
+// (valid until the next call); pmt_load_status: what loading `bytes` answers; pmt_roundtrip_equal: 1 when
+// the loaded copy has the same blob, pattern metadata and literals.
+static std::vector<uint8_t> g_saved;
+extern "C" const uint8_t *pmt_saved(pmt_lib *l, size_t *n) {
+    pm::serialize_library(l->lib, g_saved);
+    *n = g_saved.size();
+    return g_saved.data();
+}
+extern "C" int pmt_load_status(const uint8_t *bytes, size_t n) {
+    pm::CompiledLibrary c;
+    std::string err;
+    return pm::deserialize_library(bytes, n, c, err);
+}
+extern "C" int pmt_roundtrip_equal(pmt_lib *l) {
+    std::vector<uint8_t> bytes;
+    pm::serialize_library(l->lib, bytes);
+    pm::CompiledLibrary c;
+    std::string err;
+    if (pm::deserialize_library(bytes.data(), bytes.size(), c, err) != PM_OK) return 0;
+    if (c.blob != l->lib.blob || c.fold != l->lib.fold || c.patterns.size() != l->lib.patterns.size() || c.literals.size() != l->lib.literals.size()) return 0;
+    for (size_t i = 0; i < c.patterns.size(); i++) {
+        const auto &a = c.patterns[i], &b = l->lib.patterns[i];
+        if (a.id != b.id || a.name != b.name || a.severity != b.severity || a.category != b.category || a.regex != b.regex || a.meta_json != b.meta_json || a.tier != b.tier) return 0;
+    }
+    for (size_t i = 0; i < c.literals.size(); i++)
+        if (!(c.literals[i] == l->lib.literals[i])) return 0;
+    return 1;
+}

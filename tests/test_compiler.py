@@ -177,3 +177,31 @@ def test_large_library_compiles(harness):
     assert rc == 0, rep.message
     assert rep.n_patterns == 20000 and rep.n_filtered == 20000 and 15 <= rep.filter_log2_bits <= 20
     harness.L.pmt_free(h)
+
+
+def test_compiled_library_survives_a_round_trip_through_bytes(harness):
+    """8(f).2: the sync step leaves the compiled library beside the YAML.  Same blob, metadata and
+    literals after serialize -> deserialize; damaged or foreign bytes are refused."""
+    import ctypes
+    from operator_b200 import synth
+    L = harness.L
+    L.pmt_saved.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_size_t)]
+    L.pmt_saved.restype = ctypes.POINTER(ctypes.c_uint8)
+    L.pmt_load_status.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+    L.pmt_roundtrip_equal.argtypes = [ctypes.c_void_p]
+    for spec in (synth.make_library(50)[0], synth.make_library(500)[0],
+                 {"patterns": [{"id": "t", "primary_pattern": {"regex": r"\bOOM\b"}}, {"id": "u", "name": "café", "primary_pattern": {"regex": "(?i)connection refused"}}]}):
+        rc, h, rep = harness.compile(spec)
+        assert rc == 0
+        assert L.pmt_roundtrip_equal(h) == 1
+        n = ctypes.c_size_t()
+        p = L.pmt_saved(h, ctypes.byref(n))
+        data = ctypes.string_at(p, n.value)
+        assert L.pmt_load_status(data, len(data)) == 0
+        assert L.pmt_load_status(data[:-1], len(data) - 1) == -1                    # truncated
+        assert L.pmt_load_status(data[:100], 100) == -1
+        bad = bytearray(data)
+        bad[len(bad) // 2] ^= 0x40
+        assert L.pmt_load_status(bytes(bad), len(bad)) == -1                         # checksum
+        assert L.pmt_load_status(b"", 0) == -1 and L.pmt_load_status(b"x" * 64, 64) == -1
+        L.pmt_free(h)

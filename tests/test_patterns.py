@@ -70,3 +70,36 @@ def test_validate_hook_on_device(tmp_path, engine):
     root = _tree(tmp_path)
     lib = patterns.validate_patterns(engine, str(root))
     assert lib.n_patterns == 12 and lib.pattern_meta(0)["id"] == "syn-00008"   # extra.yml sorts first
+
+
+@pytest.mark.gpu
+def test_compiled_library_on_the_volume(tmp_path, engine):
+    """8(f).2: the sync hook leaves the compiled library beside the YAML; the service loads it without
+    compiling, scans with it exactly as with a freshly compiled one, and ignores it once the YAML changed."""
+    from oracle import oracle
+    root = _tree(tmp_path)
+    assert patterns.load_compiled(engine, str(root)) is None                       # nothing there yet
+    lib = patterns.validate_patterns(engine, str(root), save=True)
+    assert os.path.isfile(root / patterns.COMPILED_NAME)
+    assert [os.path.relpath(f, root) for f in patterns.discover_pattern_files(str(root))] == ["extra.yml", ".github/ci.yaml", "quarkus/core-patterns.yaml"]
+    full, wit, swit = synth.make_library(12)
+    corpus, _ = synth.make_corpus(300000, wit, swit, p_hit=3e-2)
+    want = engine.scan([corpus])
+    loaded = patterns.load_compiled(engine, str(root))                              # publishes the loaded copy
+    assert loaded is not None and loaded.n_patterns == lib.n_patterns == 12
+    assert [loaded.pattern_meta(i) for i in range(12)] == [lib.pattern_meta(i) for i in range(12)]
+    got = engine.scan([corpus])
+    assert got.n_events == want.n_events > 20
+    for name in ("pattern_index", "line_no", "ctx_first_line", "ctx_last_line", "ctx_start", "ctx_end", "score"):
+        assert (getattr(got, name) == getattr(want, name)).all(), name
+    # stale: a pattern file changed after the compile
+    with open(root / "extra.yml", "a") as f:
+        f.write("\n# touched\n")
+    assert patterns.load_compiled(engine, str(root)) is None
+    # damaged
+    patterns.validate_patterns(engine, str(root), save=True)
+    p = root / patterns.COMPILED_NAME
+    data = bytearray(p.read_bytes())
+    data[len(data) // 2] ^= 1
+    p.write_bytes(bytes(data))
+    assert patterns.load_compiled(engine, str(root)) is None
