@@ -373,3 +373,54 @@ def test_concurrent_parse_requests_share_batches(engine):
             assert o["context"]["linesAfter"] == lines[e.line_no:e.ctx_last]
         assert out[k]["summary"]["totalEvents"] == len(ev)
     assert sum(len(o["events"]) for o in out) > 200
+
+
+def test_http_front_end_speaks_the_parse_contract(engine):
+    """a3: POST /parse with application/json, as LogParserRestClient.java:21-39 sends it; 404 elsewhere,
+    400 for a malformed body, concurrent requests answered correctly."""
+    import json
+    import threading
+    import urllib.error
+    import urllib.request
+    from http.server import ThreadingHTTPServer
+    from operator_b200 import service
+    lib_json, wit, swit = synth.make_library(50)
+    engine.compile_library(lib_json).publish()
+    olib = oracle.load_library(lib_json)
+    srv = ThreadingHTTPServer(("127.0.0.1", 0), service.make_handler(engine))
+    port = srv.server_address[1]
+    t = threading.Thread(target=srv.serve_forever, daemon=True)
+    t.start()
+    try:
+        logs = [bytes(synth.make_corpus(40000 + 9000 * k, wit, swit, p_hit=3e-2, seed=70 + k)[0]) for k in range(6)]
+
+        def post(path, body):
+            req = urllib.request.Request("http://127.0.0.1:%d%s" % (port, path), data=body, headers={"Content-Type": "application/json"}, method="POST")
+            with urllib.request.urlopen(req, timeout=30) as r:
+                return r.status, r.headers.get("Content-Type"), json.loads(r.read())
+
+        out = [None] * len(logs)
+
+        def work(k):
+            body = json.dumps({"pod": {"metadata": {"name": "p%d" % k, "namespace": "n"}}, "logs": logs[k].decode(), "events": []}).encode()
+            out[k] = post("/parse", body)
+
+        ts = [threading.Thread(target=work, args=(k,)) for k in range(len(logs))]
+        for x in ts:
+            x.start()
+        for x in ts:
+            x.join()
+        for k, (status, ctype, res) in enumerate(out):
+            ev = oracle.analyze(logs[k], olib)
+            assert status == 200 and ctype == "application/json"
+            assert [(o["lineNumber"], o["matchedPattern"]["id"], o["score"]) for o in res["events"]] == [(e.line_no, olib.patterns[e.pattern].id, e.score) for e in ev]
+            assert res["summary"]["highestSeverity"] == oracle.summarize(ev, olib)["highestSeverity"] and res["metadata"]["podName"] == "p%d" % k
+        for path, body, code in (("/other", b"{}", 404), ("/parse", b"{\"logs\": \"unterminated", 400)):
+            try:
+                post(path, body)
+                raise AssertionError("expected HTTP %d" % code)
+            except urllib.error.HTTPError as e:
+                assert e.code == code
+    finally:
+        srv.shutdown()
+        srv.server_close()
