@@ -1700,6 +1700,48 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     return cudaGetLastError();
 }
 
+// Result rows and counters to pinned host memory, written by the device: the first *n_rows entries of
+// each of the ten arrays (coalesced 16-byte stores over PCIe) and the counter block.  Replaces two
+// cudaMemcpyAsync whose sizes the host would have to know - the event count never leaves the device
+// before the batch is done, so the copy is exactly as large as the result.
+__global__ void __launch_bounds__(256) k_export(EventOut src, EventOut dst, const unsigned long long *n_rows_ptr, unsigned long long cap,
+                                                const uint4 *__restrict__ ctr_src, uint4 *__restrict__ ctr_dst, int ctr_vec) {
+    const unsigned long long n = *n_rows_ptr <= cap ? *n_rows_ptr : 0;   // more rows than room: the host re-runs the resolve stage
+    const unsigned long long n8 = (n * 8 + 15) / 16, n4 = (n * 4 + 15) / 16;   // 16-byte pieces per array
+    const unsigned long long per = 4 * n8 + 6 * n4, stride = (unsigned long long)gridDim.x * blockDim.x;
+    const uint4 *s8[4] = {reinterpret_cast<const uint4 *>(src.line_start), reinterpret_cast<const uint4 *>(src.ctx_start),
+                          reinterpret_cast<const uint4 *>(src.ctx_end), reinterpret_cast<const uint4 *>(src.score)};
+    uint4 *d8[4] = {reinterpret_cast<uint4 *>(dst.line_start), reinterpret_cast<uint4 *>(dst.ctx_start), reinterpret_cast<uint4 *>(dst.ctx_end),
+                    reinterpret_cast<uint4 *>(dst.score)};
+    const uint4 *s4[6] = {reinterpret_cast<const uint4 *>(src.pod), reinterpret_cast<const uint4 *>(src.pattern), reinterpret_cast<const uint4 *>(src.line_no),
+                          reinterpret_cast<const uint4 *>(src.line_len), reinterpret_cast<const uint4 *>(src.ctx_first), reinterpret_cast<const uint4 *>(src.ctx_last)};
+    uint4 *d4[6] = {reinterpret_cast<uint4 *>(dst.pod), reinterpret_cast<uint4 *>(dst.pattern), reinterpret_cast<uint4 *>(dst.line_no),
+                    reinterpret_cast<uint4 *>(dst.line_len), reinterpret_cast<uint4 *>(dst.ctx_first), reinterpret_cast<uint4 *>(dst.ctx_last)};
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < per; i += stride) {
+        if (i < 4 * n8) {
+            const unsigned a = (unsigned)(i / n8);
+            const unsigned long long k = i - a * n8;
+            d8[a][k] = s8[a][k];
+        } else {
+            const unsigned long long j = i - 4 * n8;
+            const unsigned a = (unsigned)(j / n4);
+            const unsigned long long k = j - a * n4;
+            d4[a][k] = s4[a][k];
+        }
+    }
+    if (blockIdx.x == 0 && (int)threadIdx.x < ctr_vec) ctr_dst[threadIdx.x] = ctr_src[threadIdx.x];
+}
+
+cudaError_t launch_export(EventOut src, EventOut dst_host, const unsigned long long *n_rows_dev, unsigned long long cap, const void *ctr_dev, void *ctr_host,
+                          size_t ctr_bytes, int num_sms, cudaStream_t s) {
+    // a handful of CTAs saturates the PCIe link; more would only sit on SMs that other batches' scans wait for
+    unsigned blocks = (unsigned)std::min<unsigned long long>(8ull, (cap * 64 / 16 + 255) / 256 + 1);
+    (void)num_sms;
+    k_export<<<blocks, 256, 0, s>>>(src, dst_host, n_rows_dev, cap, reinterpret_cast<const uint4 *>(ctr_dev), reinterpret_cast<uint4 *>(ctr_host),
+                                    (int)((ctr_bytes + 15) / 16));
+    return cudaGetLastError();
+}
+
 cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
                               unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s) {
     unsigned long long *chunks = scratch, *sorted = scratch + kSmallSort;

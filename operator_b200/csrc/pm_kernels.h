@@ -131,6 +131,10 @@ cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters 
 // caller).  Used once per library to learn which literal grams are frequent in the real logs.
 cudaError_t launch_gram_profile(const uint8_t *text, unsigned long long sample_bytes, const uint32_t *keys, uint32_t log2_cap, uint32_t fold,
                                 unsigned int *counts, int num_sms, cudaStream_t s);
+// Result rows (first *n_rows_dev of each array, if <= cap) and the counter block to pinned host memory, by a kernel.
+// dst_host / ctr_host: device-visible addresses of pinned host buffers laid out like the device ones.
+cudaError_t launch_export(EventOut src, EventOut dst_host, const unsigned long long *n_rows_dev, unsigned long long cap, const void *ctr_dev, void *ctr_host,
+                          size_t ctr_bytes, int num_sms, cudaStream_t s);
 // Line table of one pod: out[i] = offset (relative to the pod) of line i, i < n_lines.
 cudaError_t launch_line_starts(const uint8_t *text, const unsigned long long *tile_prefix, unsigned long long nl_before, int n_lines,
                                unsigned long long pod_start, unsigned long long pod_eff_end, long long *out, int num_sms, cudaStream_t s);

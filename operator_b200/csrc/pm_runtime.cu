@@ -69,7 +69,7 @@ struct Pool {   // size-bucketed free list; blocks are handed back, never split
         size_t want = (bytes + 255) & ~(size_t)255;
         cudaError_t e;
         if (pinned) {
-            e = cudaHostAlloc(out, want, cudaHostAllocPortable);
+            e = cudaHostAlloc(out, want, cudaHostAllocPortable | cudaHostAllocMapped);
         } else {
             cudaSetDevice(device);
             e = cudaMalloc(out, want);
@@ -77,7 +77,7 @@ struct Pool {   // size-bucketed free list; blocks are handed back, never split
         if (e != cudaSuccess) {
             cudaGetLastError();
             trim();
-            e = pinned ? cudaHostAlloc(out, want, cudaHostAllocPortable) : cudaMalloc(out, want);
+            e = pinned ? cudaHostAlloc(out, want, cudaHostAllocPortable | cudaHostAllocMapped) : cudaMalloc(out, want);
             if (e != cudaSuccess) return fail(PM_E_NOMEM, "%s of %zu bytes: %s", pinned ? "cudaHostAlloc" : "cudaMalloc", want, cudaGetErrorString(e));
         }
         *cap = want;
@@ -715,8 +715,21 @@ int enqueue_resolve(pm_batch *b, DevWork &w, bool from_raw = false) {
     w.launches += 4;
     w.mark("resolve (plan,check,finalize)");
     CU(cudaEventRecord(w.e[6], w.stream));
-    CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
-    CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, kCtrBytes, cudaMemcpyDeviceToHost, w.stream));
+    // One batch at a time (latency mode): a small kernel writes exactly the rows there are, and the
+    // counters, straight into pinned host memory - 26 instead of 35 us at the end of the 1 GiB step,
+    // 0.25 -> 0.23 ms for a 1.4 MB request.  With several batches in flight (throughput mode) the copy
+    // engines do it instead: they cost no SM, and an SM is what the other batches are waiting for
+    // (measured: 1 % more throughput than with the kernel).  PM_RESULT_MEMCPY=1 forces the copy engines.
+    static const bool force_copy_engine = getenv("PM_RESULT_MEMCPY") != nullptr;
+    const bool copy_engine = force_copy_engine || b->ctx->devs[w.slot]->depth > 1;
+    if (copy_engine) {
+        CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
+        CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, kCtrBytes, cudaMemcpyDeviceToHost, w.stream));
+    } else {
+        // unified addressing: pinned (portable, mapped) host memory has the same address on the device
+        CU(launch_export(L.on(w.ev_soa.p), L.on(w.h_soa.p), n_unique, w.ev_cap, w.ctr.p, w.h_ctr.p, kCtrBytes, w.sms_post, w.stream));
+        w.launches += 1;
+    }
     CU(cudaEventRecord(w.e[7], w.stream));
     w.mark("result copies");
     return PM_OK;
