@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define PM_ABI_VERSION 1
+#define PM_ABI_VERSION 2
 
 typedef enum pm_status {
     PM_OK = 0,
@@ -93,8 +93,9 @@ typedef struct pm_result_view {
     /* timings of the last run, milliseconds, measured with CUDA events on the batch's streams
      * (max over devices) */
     double ms_h2d, ms_scan, ms_post, ms_d2h;
-    /* first kernel of the scan to the last result copy, one CUDA-event pair per device (includes
-     * the host round trip that sizes the sort), max over devices */
+    /* first kernel of the scan to the results on the host, one CUDA-event pair per device, max over
+     * devices (no host round trip inside unless a queue overflowed or the batch has more than 16384
+     * raw events; with several batches in flight it includes waiting for SMs other batches hold) */
     double ms_total;
     /* the combined-DFA kernel(s) alone (0 when the library has no DFA-scanned pattern) */
     double ms_dfa;
