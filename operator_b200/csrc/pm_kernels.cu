@@ -1456,7 +1456,18 @@ __global__ void __launch_bounds__(512) k_finalize(const uint8_t *__restrict__ bl
         const EvAux ax = aux[i];
         // context: leading run of STACK lines after the lines_after window
         int run = 0;
-        while (run < ax.n_stack && results[ax.item_base + run]) run++;
+        // (verdict bytes are read eight at a time, independent loads: one latency instead of one per line)
+        for (int base = 0; base < ax.n_stack; base += 8) {
+            unsigned miss = 0;
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                if (base + q < ax.n_stack && !results[ax.item_base + base + q]) miss |= 1u << q;
+            if (miss) {
+                run = base + __ffs(miss) - 1;
+                break;
+            }
+            run = min(base + 8, ax.n_stack);
+        }
         int64_t ctx_end = ax.ctx_end;
         if (run > 0) {
             const Item it = items[ax.item_base + run - 1];
@@ -1469,11 +1480,13 @@ __global__ void __launch_bounds__(512) k_finalize(const uint8_t *__restrict__ bl
             const SecDesc sd = sds[pd.sec_first + j];
             const int cnt = 2 * sd.window + 1;
             int best = -1;
-            for (int idx = 0; idx < cnt; idx++)
-                if (results[off + idx]) {
-                    best = (idx + 1) >> 1;   // idx ascending = distance non-decreasing
-                    break;
-                }
+            for (int base = 0; base < cnt && best < 0; base += 8) {
+                unsigned hit = 0;
+#pragma unroll
+                for (int q = 0; q < 8; q++)
+                    if (base + q < cnt && results[off + base + q]) hit |= 1u << q;
+                if (hit) best = (base + __ffs(hit)) >> 1;   // first hit idx = base + ffs - 1; distance (idx + 1) >> 1; idx ascending = distance non-decreasing
+            }
             if (best >= 0) {
                 double term = __dmul_rn(sd.weight, __dsub_rn(1.0, __ddiv_rn((double)best, (double)(sd.window + 1))));
                 acc = __dadd_rn(acc, term);
