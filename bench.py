@@ -33,7 +33,6 @@ CORPUS_BYTES = 1 << 30
 N_PATTERNS = 500
 P_HIT = 1e-3
 CPU_SAMPLE_BYTES = 1 << 30      # the whole config-2 corpus: ~15 s on 16 cores, no extrapolation needed
-REF_STEP_BYTES = 64 << 20
 
 
 def parse_args():
@@ -47,6 +46,7 @@ def parse_args():
     ap.add_argument("--depth", type=int, default=5, help="batches in flight per GPU in the throughput legs (pm_set_pipeline); 1 = one at a time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--ref-budget-s", type=float, default=150.0, help="--impl reference: wall-clock budget for warm-up + timed steps")
     return ap.parse_args()
 
 
@@ -111,7 +111,8 @@ def peak_hbm():
 
 
 def cpu_scan(corpus, lib_json, nbytes, threads):
-    """The reference-style CPU loop on `nbytes` of the corpus; returns (seconds, bytes, matches)."""
+    """The reference-style CPU loop on `nbytes` of the corpus; returns (seconds, bytes, matches,
+    sorted (line_no, pattern_index) pairs or None)."""
     import numpy as np
     from oracle import pcre2_oracle as po
     sample = corpus[:nbytes]
@@ -120,40 +121,64 @@ def cpu_scan(corpus, lib_json, nbytes, threads):
     lib = po.Pcre2Library([p["primary_pattern"]["regex"] for p in lib_json["patterns"]])
     t0 = time.perf_counter()
     starts, lens = po.split(sample)
-    _, _, total = po.scan(lib, sample, starts, lens, threads=threads)
+    lines, pats, total = po.scan(lib, sample, starts, lens, threads=threads)
     dt = time.perf_counter() - t0
     lib.close()
-    return dt, cut, total
+    pairs = None
+    if total == lines.size:   # all (line, pattern) matches fit the output arrays: usable as the full-size parity reference
+        pairs = np.stack([lines.astype(np.int64) + 1, pats.astype(np.int64)], axis=1)
+        pairs = pairs[np.lexsort((pairs[:, 1], pairs[:, 0]))]
+    return dt, cut, total, pairs
+
+
+def workload_config(args, world):
+    """The `config` object: identical in both arms (ours and --impl reference)."""
+    return {"workload": "configs[1]: 1 GiB synthetic crash-log corpus vs 500-pattern library, per GPU", "corpus_bytes": args.corpus_bytes,
+            "patterns": args.patterns, "p_hit": P_HIT, "parallelism": "pod-sharded x%d, no collective" % world,
+            "l2": "input (1 GiB per GPU) is larger than the 126 MB L2; no flush between iterations"}
 
 
 def run_reference(args, rank, world):
     """--impl reference: the reference's own CPU shape for this path (split lines, per line x per
-    pattern unanchored regex search) on all host cores.  The JVM engine (java.util.regex) is not in
-    this image; PCRE2-JIT stands in (oracle/scan_pcre2.c) -- kind "port"."""
+    pattern unanchored regex search) on all host cores, on the SAME corpus, pattern count, steps and
+    warm-up as our arm.  The JVM engine (java.util.regex) is not in this image; PCRE2-JIT stands in
+    (oracle/scan_pcre2.c) -- kind "port".  One step over 1 GiB takes ~14 s on 16 threads, so the run is
+    capped by a wall-clock budget (--ref-budget-s, default 150 s): steps beyond it are not run and the
+    line says so."""
     if rank != 0:
         return
     import numpy as np
     from operator_b200 import synth
     lib_json, wit, swit = synth.make_library(args.patterns)
-    step_bytes = min(REF_STEP_BYTES, args.corpus_bytes)
-    corpus, _ = synth.make_corpus(step_bytes, wit, swit, p_hit=P_HIT)
+    corpus, _ = synth.make_corpus(args.corpus_bytes, wit, swit, p_hit=P_HIT)
     cores = os.cpu_count() or 1
-    for _ in range(min(args.warmup, 1)):
-        cpu_scan(corpus, lib_json, min(step_bytes, 2 << 20), cores)
-    t_total, b_total = 0.0, 0
-    steps = max(1, min(args.steps, 5))
-    for _ in range(steps):
-        dt, nb, _ = cpu_scan(corpus, lib_json, step_bytes, cores)
+    t_begin = time.perf_counter()
+    budget = args.ref_budget_s
+    warm_done = 0
+    t_step_est = None
+    for _ in range(args.warmup):
+        if t_step_est is not None and (time.perf_counter() - t_begin) + 2 * t_step_est > budget:   # keep room for one timed step
+            break
+        dt, _, _, _ = cpu_scan(corpus, lib_json, args.corpus_bytes, cores)
+        t_step_est = dt
+        warm_done += 1
+    t_total, b_total, steps = 0.0, 0, 0
+    for _ in range(max(1, args.steps)):
+        if steps >= 1 and (time.perf_counter() - t_begin) + t_total / steps > budget:
+            break
+        dt, nb, _, _ = cpu_scan(corpus, lib_json, args.corpus_bytes, cores)
         t_total += dt
         b_total += nb
+        steps += 1
     gbs = b_total / t_total / 1e9
-    sample = "%d steps x first %d MiB of the config-2 corpus, %d patterns, PCRE2-JIT, %d threads" % (steps, step_bytes >> 20, args.patterns, cores)
+    sample = "%d steps x the whole %d MiB config-2 corpus, %d patterns, PCRE2-JIT, %d threads" % (steps, args.corpus_bytes >> 20, args.patterns, cores)
     print(json.dumps({
         "impl": "reference", "metric": "log_scan_throughput", "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * t_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[1]: 1 GiB synthetic crash-log corpus vs 500-pattern library (bounded sample per step)",
-                   "patterns": args.patterns, "p_hit": P_HIT, "sample_bytes_per_step": step_bytes},
+        "warmup": warm_done, "ms_per_step": 1e3 * t_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic", "config": workload_config(args, world),
+        "steps_requested": args.steps, "warmup_requested": args.warmup,
+        "budget": {"seconds": budget, "capped": steps < args.steps or warm_done < args.warmup,
+                   "note": "a step scans the whole corpus; steps and warm-up beyond the wall-clock budget are not run"},
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -186,7 +211,7 @@ def main():
     visible = os.environ.get("CUDA_VISIBLE_DEVICES")
     gpu_index = visible.split(",")[local] if visible else str(local)
     eng = Engine(devices=[local])
-    eng.compile_library(lib_json).publish()
+    lib_report = eng.compile_library(lib_json).publish().report
     pinned = eng.pinned(args.corpus_bytes)
     corpus, n_lines = synth.make_corpus(args.corpus_bytes, wit, swit, p_hit=P_HIT, first_line=rank << 36, out=pinned.array)
     nbytes = int(corpus.size)
@@ -217,6 +242,7 @@ def main():
     sync_all()
     n_events, n_cand, n_ver = r.n_events, r.n_candidates, r.n_verified
     want_events = int(r.n_events)
+    gpu_pairs = np.stack([r.line_no.astype(np.int64), r.pattern_index.astype(np.int64)], axis=1)   # a copy: the views die with the batch
     d2h_bytes = int(r.n_events) * 64 + 64
     b.release()
 
@@ -365,6 +391,7 @@ def main():
     total_bytes = dist.sum_over_ranks(nbytes, dev)
     h2d_ms = dist.max_over_ranks(ms_h2d / e2e_steps, dev)
 
+    parity_failed = False
     if rank == 0:
         peak, peak_src = peak_hbm()
         achieved = nbytes / (scan_ms * 1e-3) / 1e9          # per GPU: the kernel's own launch
@@ -378,12 +405,10 @@ def main():
             "metric": "log_scan_throughput", "value": total_bytes / (step_ms * 1e-3) / 1e9, "unit": "GB/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "configs[1]: 1 GiB synthetic crash-log corpus vs 500-pattern library, per GPU", "corpus_bytes_per_gpu": nbytes,
-                       "lines_per_gpu": n_lines, "patterns": args.patterns, "p_hit": P_HIT, "parallelism": "pod-sharded x%d, no collective" % world,
-                       "batches_in_flight_per_gpu": depth,
-                       "l2": "input (1 GiB per GPU) is larger than the 126 MB L2; no flush between iterations",
-                       "events_per_step": int(n_events), "filter_candidates_per_step": int(n_cand),
-                       "literal_confirms_per_step": int(n_ver)},
+            "config": workload_config(args, world),
+            "workload_stats": {"corpus_bytes_per_gpu": nbytes, "lines_per_gpu": n_lines, "batches_in_flight_per_gpu": depth,
+                               "events_per_step": int(n_events), "filter_candidates_per_step": int(n_cand), "literal_confirms_per_step": int(n_ver),
+                               "library": {k: lib_report[k] for k in ("n_patterns", "n_filtered", "n_dfa_scanned", "dfa_groups", "n_grams", "filter_log2_bits", "blob_bytes")}},
             "e2e": {"value": total_bytes / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": nbytes + 64, "d2h_bytes_per_step": d2h_bytes,
                     "h2d_ms_per_copy": h2d_ms, "requests_in_flight": e2e_depth, "steps": e2e_steps,
                     "note": "PCIe-bound: with 2 requests in flight their host-to-device copies share the link (each takes ~2x as long), "
@@ -391,6 +416,8 @@ def main():
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k_scan", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_nominal_8TBs": achieved / 8000.0, "peak_source": peak_src, "traffic": traffic,
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one k_scan launch from the ncu --set full capture under profiles/ "
+                                           "(k_scan_traffic.json names it); not measured in this run",
                          "algorithmic_bytes_per_launch": nbytes, "avg_launch_ms": scan_ms,
                          "timed": "CUDA events around each k_scan launch, %d launches, kernel alone on the GPU (one batch at a time)" % serial_steps,
                          "whole_step_frac": (nbytes / (step_ms * 1e-3) / 1e9) / peak},
@@ -405,16 +432,27 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            dt, nb, _ = cpu_scan(corpus, lib_json, min(CPU_SAMPLE_BYTES, nbytes), cores)
+            dt, nb, n_match, cpu_pairs = cpu_scan(corpus, lib_json, min(CPU_SAMPLE_BYTES, nbytes), cores)
             out["cpu_baseline"] = {"value": nb / dt / 1e9, "unit": "GB/s", "cores": cores, "kind": "port",
                                    "sample": "first %d MiB of the same corpus, all %d patterns, per line x per pattern PCRE2-JIT search "
                                              "(JVM unavailable on this box), %d threads, %.1f s" % (nb >> 20, args.patterns, cores, dt)}
+            # Full-size parity of the headline configuration: the CPU loop has just produced every (line, pattern)
+            # match of the whole corpus; the GPU step's events must be exactly those pairs.
+            if cpu_pairs is not None and nb == nbytes:
+                equal = cpu_pairs.shape == gpu_pairs.shape and bool(np.array_equal(cpu_pairs, gpu_pairs))
+                out["parity_check"] = {"pairs": int(cpu_pairs.shape[0]), "gpu_pairs": int(gpu_pairs.shape[0]), "equal": equal,
+                                       "what": "(line_no, pattern_index) of every event of one timed step vs the PCRE2 loop over the same %d bytes" % nb}
+                parity_failed = not equal
+            else:
+                out["parity_check"] = {"pairs": int(n_match), "equal": None, "what": "not comparable: the CPU leg did not cover the whole corpus"}
         print(json.dumps(out))
     pinned.free()
     eng.close()
     if world > 1:
         import torch.distributed as td
         td.destroy_process_group()
+    if parity_failed:
+        raise SystemExit("bench.py: the GPU events differ from the CPU loop's matches on the full corpus (parity_check.equal = false)")
 
 
 if __name__ == "__main__":

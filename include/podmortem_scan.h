@@ -181,7 +181,11 @@ int64_t pm_batch_line_index(pm_batch *, int pod, int64_t *out, int64_t cap);
  *     (different streams, different host threads) race on it and corrupt each other's result.
  *     Serialise them: same stream, or an event between them;
  *   - the first call on each GPU looks up the array's device address (with that GPU current);
- *     make that first call outside any stream capture.
+ *     make that first call outside any stream capture.  The address is kept for the life of the
+ *     process: after a cudaDeviceReset() on that GPU it is stale, so do not call this entry point
+ *     again in a process that reset the device;
+ *   - a CUDA error left pending on the calling thread by an earlier, unrelated call is neither
+ *     cleared nor blamed on this call: the entry point returns PM_E_CUDA and launches nothing.
  * d_text, d_line_start and d_n_lines are DEVICE pointers supplied by the caller; the current
  * device must be the one they live on.  d_line_start[i] receives the byte offset of line i for
  * i < min(*d_n_lines, cap), with the line model of SPEC.md section 2 (the same table

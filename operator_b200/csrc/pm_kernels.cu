@@ -19,6 +19,9 @@
 
 namespace pm {
 
+thread_local void (*g_stage_mark)(void *, const char *) = nullptr;
+thread_local void *g_stage_mark_arg = nullptr;
+
 namespace {
 
 constexpr unsigned FULL = 0xFFFFFFFFu;
@@ -67,6 +70,72 @@ __device__ __forceinline__ unsigned lanemask_lt() {
     unsigned m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
+}
+
+// ------------------------------------------------------------------------------------ confirm
+// What a warp needs to turn one filter hit into verify tasks.
+struct ConfirmParams {
+    const uint8_t *text;
+    unsigned long long total;
+    const uint32_t *gkeys, *gfirst, *gcount;
+    const Probe *probes;
+    const uint8_t *litpool;
+    uint32_t log2_cap, fold;
+    unsigned long long *tasks;
+    unsigned long long task_cap;
+};
+
+// One filter hit, the whole warp: (16-byte group, mask of its 4 aligned words) -> exact gram lookup
+// (warp-uniform) -> every lane takes one probe of the gram's probe list and compares its literal
+// -> (position, pattern) verify tasks.
+__device__ __forceinline__ void confirm_candidate(const ConfirmParams &cp, ScanCounters *ctr, unsigned long long group, uint32_t m4) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t cap_mask = (1u << cp.log2_cap) - 1u;
+    while (m4) {
+        const int k = __ffs(m4) - 1;
+        m4 &= m4 - 1;
+        const unsigned long long p = group * 16 + k * 4;
+        uint32_t g = *reinterpret_cast<const uint32_t *>(cp.text + p);
+        if (cp.fold) g |= 0x20202020u;
+        uint32_t slot = gram_table_slot(g, cp.log2_cap);
+        uint32_t key;
+        while ((key = __ldg(cp.gkeys + slot)) != g && key != kGramEmpty) slot = (slot + 1) & cap_mask;
+        if (key != g) continue;   // filter collision (warp-uniform)
+        const uint32_t q0 = __ldg(cp.gfirst + slot), qn = __ldg(cp.gcount + slot);
+        for (uint32_t qb = 0; qb < qn; qb += 32) {
+            const uint32_t q = qb + lane;
+            bool eq = false;
+            Probe pr;
+            if (q < qn) {
+                pr = cp.probes[q0 + q];
+                if (p >= kHeaderBytes + pr.gram_off && p - pr.gram_off + pr.lit_len <= cp.total) {
+                    // word-wise: literal and case mask are 4-byte aligned and 0xFF-padded (pm_library.cc),
+                    // the text word at an arbitrary offset comes from two aligned words and a funnel shift
+                    const unsigned long long st = p - pr.gram_off;
+                    const uint32_t n_words = (pr.lit_len + 3u) >> 2, sh = (uint32_t)(st & 3) * 8;
+                    const uint32_t *lit = reinterpret_cast<const uint32_t *>(cp.litpool + pr.lit_off), *msk = lit + n_words;
+                    const uint32_t *tw = reinterpret_cast<const uint32_t *>(cp.text + (st & ~3ull));
+                    uint32_t lo = tw[0];
+                    eq = true;
+                    for (uint32_t j = 0; j < n_words; j++) {
+                        const uint32_t hi = tw[j + 1];
+                        if ((__funnelshift_r(lo, hi, sh) | msk[j]) != lit[j]) {
+                            eq = false;
+                            break;
+                        }
+                        lo = hi;
+                    }
+                }
+            }
+            if (eq) {
+                unsigned long long at = atomicAdd(&ctr->n_verified, 1ull);
+                if (at < cp.task_cap)
+                    cp.tasks[at] = (p << kPatternBits) | pr.pattern;
+                else
+                    ctr->raw_overflow = 1;
+            }
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------ k_scan
@@ -138,6 +207,11 @@ __device__ __forceinline__ uint32_t scan_word(uint32_t w, const ScanConsts &k, u
     return shr_wrap(word, h);
 }
 
+// Confirming the hits inside this kernel (so that k_confirm drops off the post-scan chain) was measured
+// twice in round 2 and not adopted: in the streaming loop every confirmation delayed its warp's last
+// tile (warps own a fixed set of tiles; 179 -> 204 us), and as a per-CTA phase after the loop, one thread
+// per queued hit, it took 33 us plus 14 us from the changed loop code (179 -> 226 us) - against the
+// 17 us of the separate launch, whose ~16 k warps run one hit each.
 template <int BITS, bool FOLD>
 __global__ void __launch_bounds__(kScanThreads, 1)
 k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g, const uint4 *__restrict__ bitmap2_g,
@@ -268,11 +342,14 @@ k_scan_nl_only(const uint4 *__restrict__ text, unsigned long long n_tiles, uint3
 }
 
 // ------------------------------------------------------------------------------------ prefix
-constexpr int kPrefThreads = 1024, kPrefItems = 4, kPrefBlock = kPrefThreads * kPrefItems;
+// 256-thread CTAs on purpose: these kernels run on a side stream while k_verify (1536 resident threads
+// per SM) owns the GPU, and a 1024-thread CTA would find no SM to start on until that kernel drains.
+constexpr int kPrefThreads = 256, kPrefItems = 16, kPrefBlock = kPrefThreads * kPrefItems;
 
+// Exclusive scan over the CTA (any multiple of 32 threads up to 1024); *total receives the sum.
 __device__ __forceinline__ unsigned long long block_exclusive_scan(unsigned long long v, unsigned long long *total) {
     __shared__ unsigned long long wsum[32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     unsigned long long inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -282,7 +359,7 @@ __device__ __forceinline__ unsigned long long block_exclusive_scan(unsigned long
     if (lane == 31) wsum[warp] = inc;
     __syncthreads();
     if (warp == 0) {
-        unsigned long long w = wsum[lane], winc = w;
+        unsigned long long w = lane < n_warps ? wsum[lane] : 0ull, winc = w;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             unsigned long long y = __shfl_up_sync(FULL, winc, o);
@@ -297,42 +374,58 @@ __device__ __forceinline__ unsigned long long block_exclusive_scan(unsigned long
     return r;
 }
 
+// Sum of one block of kPrefBlock tile counts.
 __global__ void __launch_bounds__(kPrefThreads) k_prefix_partial(const uint32_t *__restrict__ in, unsigned long long n, unsigned long long *__restrict__ block_sums) {
-    unsigned long long i0 = (unsigned long long)blockIdx.x * kPrefBlock + threadIdx.x * kPrefItems, s = 0;
+    const unsigned long long i0 = (unsigned long long)blockIdx.x * kPrefBlock + threadIdx.x * 4;
+    unsigned long long s = 0;
 #pragma unroll
-    for (int k = 0; k < kPrefItems; k++)
-        if (i0 + k < n) s += in[i0 + k];
+    for (int r = 0; r < kPrefItems / 4; r++) {   // coalesced 16-byte loads (n_tiles counts are padded to a multiple of 4 by the caller's buffer)
+        const unsigned long long i = i0 + (unsigned long long)r * kPrefThreads * 4;
+        if (i + 4 <= n) {
+            const uint4 x = *reinterpret_cast<const uint4 *>(in + i);
+            s += (unsigned long long)x.x + x.y + x.z + x.w;
+        } else {
+            for (int k = 0; k < 4; k++)
+                if (i + k < n) s += in[i + k];
+        }
+    }
     __shared__ unsigned long long tot;
     block_exclusive_scan(s, &tot);
     if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
 }
 
-__global__ void __launch_bounds__(kPrefThreads) k_prefix_blocks(unsigned long long *block_sums, unsigned long long n_blocks) {
-    __shared__ unsigned long long tot;
-    unsigned long long carry = 0;
-    for (unsigned long long b0 = 0; b0 < n_blocks; b0 += kPrefThreads) {
-        unsigned long long i = b0 + threadIdx.x, v = i < n_blocks ? block_sums[i] : 0;
-        unsigned long long ex = block_exclusive_scan(v, &tot);
-        if (i < n_blocks) block_sums[i] = carry + ex;
-        carry += tot;
-        __syncthreads();
-    }
-}
-
+// Tile prefix of one block: every CTA first adds up the sums of the blocks in front of it (a few
+// hundred values even for a full device), then scans its own counts.  One launch instead of a
+// single-CTA scan of the block sums followed by the per-block pass.
 __global__ void __launch_bounds__(kPrefThreads) k_prefix_final(const uint32_t *__restrict__ in, unsigned long long n, const unsigned long long *__restrict__ block_sums,
                                                                 unsigned long long *__restrict__ out) {
-    unsigned long long i0 = (unsigned long long)blockIdx.x * kPrefBlock + threadIdx.x * kPrefItems, s = 0;
+    __shared__ unsigned long long base_s;
+    unsigned long long mine = 0;
+    for (unsigned b = threadIdx.x; b < blockIdx.x; b += kPrefThreads) mine += block_sums[b];
+    block_exclusive_scan(mine, &base_s);
+    // thread t owns kPrefItems consecutive counts
+    const unsigned long long i0 = (unsigned long long)blockIdx.x * kPrefBlock + (unsigned long long)threadIdx.x * kPrefItems;
     uint32_t x[kPrefItems];
+    unsigned long long s = 0;
 #pragma unroll
-    for (int k = 0; k < kPrefItems; k++) {
-        x[k] = (i0 + k < n) ? in[i0 + k] : 0;
-        s += x[k];
+    for (int k = 0; k < kPrefItems; k += 4) {
+        if (i0 + k + 4 <= n) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(in + i0 + k);
+            x[k] = v.x, x[k + 1] = v.y, x[k + 2] = v.z, x[k + 3] = v.w;
+        } else {
+            for (int q = 0; q < 4; q++) x[k + q] = (i0 + k + q < n) ? in[i0 + k + q] : 0;
+        }
+        s += (unsigned long long)x[k] + x[k + 1] + x[k + 2] + x[k + 3];
     }
-    unsigned long long ex = block_exclusive_scan(s, nullptr) + block_sums[blockIdx.x];
+    unsigned long long ex = block_exclusive_scan(s, nullptr) + base_s;
 #pragma unroll
-    for (int k = 0; k < kPrefItems; k++) {
-        if (i0 + k < n) out[i0 + k] = ex;
-        ex += x[k];
+    for (int k = 0; k < kPrefItems; k += 2) {
+        if (i0 + k + 2 <= n) {
+            *reinterpret_cast<ulonglong2 *>(out + i0 + k) = make_ulonglong2(ex, ex + x[k]);
+        } else if (i0 + k < n) {
+            out[i0 + k] = ex;
+        }
+        ex += (unsigned long long)x[k] + x[k + 1];
     }
 }
 
@@ -448,70 +541,22 @@ __global__ void k_pods(const uint8_t *text, const unsigned long long *tile_prefi
 }
 
 // ------------------------------------------------------------------------------------ k_confirm
-__global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h,
-                                                 FilterView fv, const unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+// Stage 1 of the confirmation: candidate -> exact gram -> literal.  Survivors become verify
+// tasks (position, pattern).  One WARP per candidate: the gram lookup is uniform, then every
+// lane takes one probe of the gram's probe list and compares its literal.  (One thread per
+// candidate made each warp serialise 32 unrelated probe/compare loops.)
+__global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ text, unsigned long long total, FilterView fv,
+                                                 const unsigned long long *__restrict__ cand, unsigned long long cand_cap,
                                                  unsigned long long *__restrict__ tasks, unsigned long long task_cap, ScanCounters *ctr) {
-    // Stage 1 of the confirmation: candidate -> exact gram -> literal.  Survivors become verify
-    // tasks (position, pattern).  One WARP per candidate: the gram lookup is uniform, then every
-    // lane takes one probe of the gram's probe list and compares its literal.  (One thread per
-    // candidate made each warp serialise 32 unrelated probe/compare loops.)
     if (ctr->cand_overflow) return;   // the host reruns the scan with a larger queue
-    const int lane = threadIdx.x & 31;
     const unsigned long long n = ctr->n_cand < cand_cap ? ctr->n_cand : cand_cap;
-    const uint32_t *gk = fv.gkeys, *gf = fv.gfirst, *gc = fv.gcount;
-    const Probe *probes = fv.probes;
-    const uint8_t *litpool = fv.litpool;
-    const uint32_t cap_mask = (1u << fv.log2_cap) - 1u;
     const unsigned long long n_warps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    ConfirmParams cp;
+    cp.text = text, cp.total = total, cp.gkeys = fv.gkeys, cp.gfirst = fv.gfirst, cp.gcount = fv.gcount, cp.probes = fv.probes, cp.litpool = fv.litpool;
+    cp.log2_cap = fv.log2_cap, cp.fold = fv.fold, cp.tasks = tasks, cp.task_cap = task_cap;
     for (unsigned long long i = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += n_warps) {
-        unsigned long long e = cand[i];
-        unsigned long long group = e >> 4;
-        uint32_t m4 = (uint32_t)(e & 15u);
-        while (m4) {
-            int k = __ffs(m4) - 1;
-            m4 &= m4 - 1;
-            unsigned long long p = group * 16 + k * 4;
-            uint32_t g = *reinterpret_cast<const uint32_t *>(text + p);
-            if (fv.fold) g |= 0x20202020u;
-            uint32_t slot = gram_table_slot(g, fv.log2_cap);
-            uint32_t key;
-            while ((key = gk[slot]) != g && key != kGramEmpty) slot = (slot + 1) & cap_mask;
-            if (key != g) continue;   // filter collision (warp-uniform)
-            const uint32_t q0 = gf[slot], qn = gc[slot];
-            for (uint32_t qb = 0; qb < qn; qb += 32) {
-                const uint32_t q = qb + lane;
-                bool eq = false;
-                Probe pr;
-                if (q < qn) {
-                    pr = probes[q0 + q];
-                    if (p >= kHeaderBytes + pr.gram_off && p - pr.gram_off + pr.lit_len <= total) {
-                        // word-wise: literal and case mask are 4-byte aligned and 0xFF-padded (pm_library.cc),
-                        // the text word at an arbitrary offset comes from two aligned words and a funnel shift
-                        const unsigned long long st = p - pr.gram_off;
-                        const uint32_t n_words = (pr.lit_len + 3u) >> 2, sh = (uint32_t)(st & 3) * 8;
-                        const uint32_t *lit = reinterpret_cast<const uint32_t *>(litpool + pr.lit_off), *msk = lit + n_words;
-                        const uint32_t *tw = reinterpret_cast<const uint32_t *>(text + (st & ~3ull));
-                        uint32_t lo = tw[0];
-                        eq = true;
-                        for (uint32_t j = 0; j < n_words; j++) {
-                            const uint32_t hi = tw[j + 1];
-                            if ((__funnelshift_r(lo, hi, sh) | msk[j]) != lit[j]) {
-                                eq = false;
-                                break;
-                            }
-                            lo = hi;
-                        }
-                    }
-                }
-                if (eq) {
-                    unsigned long long at = atomicAdd(&ctr->n_verified, 1ull);
-                    if (at < task_cap)
-                        tasks[at] = (p << kPatternBits) | pr.pattern;
-                    else
-                        ctr->raw_overflow = 1;
-                }
-            }
-        }
+        const unsigned long long e = cand[i];
+        confirm_candidate(cp, ctr, e >> 4, (uint32_t)(e & 15u));
     }
 }
 
@@ -546,21 +591,35 @@ __device__ __forceinline__ void warp_touch_table(const uint16_t *tab, uint32_t b
     asm volatile("" ::"r"(sink));   // keeps the loads; nothing waits for them here
 }
 
+// TAB_SHARED: `tab` is the warp's copy of the table in shared memory (k_verify stages tables that fit
+// its per-warp budget: a lookup then costs one shared-memory read, ~25 cycles, and never misses; through
+// L1 the same walk saw a 56 % hit rate, 48 warps per SM with a table each, and ~70 % of the kernel's
+// stall samples sat on these loads).
+template <bool TAB_SHARED>
 __device__ __forceinline__ uint32_t warp_walk_line(const uint8_t *__restrict__ text, unsigned long long a, unsigned long long b, const uint16_t *__restrict__ tab,
                                                    uint32_t stride, uint32_t acc, uint32_t dead, uint32_t mid, const uint8_t *__restrict__ gcm,
                                                    uint8_t *cmap_s, uint8_t *cls) {
     const int lane = threadIdx.x & 31;
     uint32_t s = 0;
+    const uint32_t tab_saddr = TAB_SHARED ? (uint32_t)__cvta_generic_to_shared(tab) : 0u;
+    auto next = [&](uint32_t st, uint32_t c) -> uint32_t {
+        if (TAB_SHARED) {
+            unsigned short v;
+            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(tab_saddr + 2u * (st * stride + c)));
+            return v;
+        }
+        return __ldg(tab + (st * stride + c));
+    };
     auto walk = [&](uint32_t s0, uint32_t p0, uint32_t p1) {
         uint32_t k = p0;
         for (; k + 4 <= p1 && s0 != acc && s0 != dead; k += 4) {
             const uint32_t c0 = cls[k], c1 = cls[k + 1], c2 = cls[k + 2], c3 = cls[k + 3];
-            s0 = __ldg(tab + (s0 * stride + c0));
-            s0 = __ldg(tab + (s0 * stride + c1));
-            s0 = __ldg(tab + (s0 * stride + c2));
-            s0 = __ldg(tab + (s0 * stride + c3));
+            s0 = next(s0, c0);
+            s0 = next(s0, c1);
+            s0 = next(s0, c2);
+            s0 = next(s0, c3);
         }
-        for (; k < p1 && s0 != acc && s0 != dead; k++) s0 = __ldg(tab + (s0 * stride + cls[k]));
+        for (; k < p1 && s0 != acc && s0 != dead; k++) s0 = next(s0, cls[k]);
         return s0;
     };
     bool have_cmap = false;
@@ -622,7 +681,9 @@ constexpr int kVerifyWarps = 4;
 
 __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t *__restrict__ text, unsigned long long total, const uint8_t *__restrict__ blob, BlobHeader h, PodTable pt,
                                                               const unsigned long long *__restrict__ tasks, unsigned long long task_cap,
-                                                              unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr) {
+                                                              unsigned long long *__restrict__ raw, unsigned long long raw_cap, ScanCounters *ctr,
+                                                              uint32_t table_cap) {
+    extern __shared__ __align__(16) unsigned char s_tables[];   // kVerifyWarps x table_cap bytes: each warp's copy of its task's table
     __shared__ __align__(16) uint8_t s_cmap[kVerifyWarps][256];
     __shared__ __align__(16) uint8_t s_cls[kVerifyWarps][kWalkPiece];
     if (ctr->cand_overflow || ctr->raw_overflow) return;
@@ -644,7 +705,16 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
         // (opaque to the compiler from here on: otherwise it re-derives the pointer from the uniform base
         // and the 32-bit table offset inside every lookup, a 64-bit carry chain of five instructions)
         asm volatile("" : "+l"(gtab));
-        warp_touch_table(gtab, (uint32_t)ud.nstates * ud.stride * 2u);
+        const uint32_t tbytes = (uint32_t)ud.nstates * ud.stride * 2u;
+        const bool staged = tbytes <= table_cap;   // warp-uniform
+        unsigned char *stab = s_tables + (size_t)warp * table_cap;
+        if (staged) {   // tables start 16-byte aligned in the blob and are followed by at least their padding
+            __syncwarp();
+            for (uint32_t off = lane * 16u; off < tbytes; off += 512u)
+                *reinterpret_cast<uint4 *>(stab + off) = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(gtab) + off));
+        } else {
+            warp_touch_table(gtab, tbytes);
+        }
         uint32_t m = newline_mask16(around);
         if (lane == 16) m &= ~((1u << (p - p16)) - 1u);          // forward search starts at p
         unsigned has = __ballot_sync(FULL, m != 0);
@@ -690,8 +760,10 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
         const unsigned long long lend = strip_cr(text, pt, ls, le);
         // ---- the walk (class map and first piece of the line travel together)
         const uint32_t stride = ud.stride, acc = ud.accept_state;
-        uint32_t st = warp_walk_line(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, blob + h.off_classmaps + ud.classmap_off,
-                                     s_cmap[warp], s_cls[warp]);
+        uint32_t st = staged ? warp_walk_line<true>(text, ls, lend, reinterpret_cast<const uint16_t *>(stab), stride, acc, ud.dead_state, ud.mid_state,
+                                                    blob + h.off_classmaps + ud.classmap_off, s_cmap[warp], s_cls[warp])
+                             : warp_walk_line<false>(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, blob + h.off_classmaps + ud.classmap_off,
+                                                     s_cmap[warp], s_cls[warp]);
         if (st != acc) st = __ldg(gtab + (st * stride + stride - 1));
         if (lane == 0) {
             if (st == acc) {
@@ -1134,6 +1206,24 @@ __global__ void __launch_bounds__(1024) k_sort_unique(const unsigned long long *
     }
 }
 
+// Rank of every raw key in the sorted, de-duplicated array.  Runs on the sort's stream, beside
+// k_plan / k_check, so that k_finalize (on the main chain) reads its row index instead of doing a
+// 13-step binary search through L2 per key.
+__global__ void __launch_bounds__(256) k_rank(const unsigned long long *__restrict__ raw, const ScanCounters *ctr, unsigned long long raw_cap,
+                                              const unsigned long long *__restrict__ uniq, const unsigned long long *n_unique_ptr, uint32_t *__restrict__ rank) {
+    if (sort_too_big(ctr, raw_cap)) return;
+    const unsigned n = (unsigned)ctr->n_raw, nu = (unsigned)*n_unique_ptr;
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long key = raw[i];
+    unsigned lo = 0, hi = nu;   // lower bound; the key is present
+    while (lo < hi) {
+        const unsigned mid = (lo + hi) >> 1;
+        if (uniq[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    rank[i] = lo;
+}
+
 // ------------------------------------------------------------------------------------ resolve (a12 + a13)
 // Three kernels, so that the expensive part -- walking context lines through the STACK and
 // secondary-pattern DFAs -- is balanced over the whole GPU instead of serialised per event:
@@ -1433,7 +1523,7 @@ __global__ void __launch_bounds__(512) k_finalize(const uint8_t *__restrict__ bl
                                                   const unsigned long long *n_keys_ptr, const unsigned long long *__restrict__ uniq,
                                                   const unsigned long long *n_unique_ptr, unsigned long long ev_cap, EventOut out,
                                                   const Item *__restrict__ items, const unsigned char *__restrict__ results,
-                                                  const EvAux *__restrict__ aux, const PodTable pt, ResolveCounters *ctr) {
+                                                  const EvAux *__restrict__ aux, const PodTable pt, ResolveCounters *ctr, const uint32_t *__restrict__ rank) {
     if (ctr->overflow) return;
     const unsigned long long n_keys = *n_keys_ptr, n_unique = *n_unique_ptr;
     if (n_unique > ev_cap) {
@@ -1444,12 +1534,17 @@ __global__ void __launch_bounds__(512) k_finalize(const uint8_t *__restrict__ bl
     const SecDesc *sds = reinterpret_cast<const SecDesc *>(blob + h.off_secondaries);
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_keys; i += (unsigned long long)gridDim.x * blockDim.x) {
         const unsigned long long key = keys[i];
-        unsigned long long lo = 0, hi = n_unique;            // lower bound; the key is present
-        while (lo < hi) {
-            unsigned long long mid = (lo + hi) >> 1;
-            if (uniq[mid] < key) lo = mid + 1; else hi = mid;
+        unsigned long long ev;
+        if (rank) {                                          // keys[] is the raw queue and k_rank has placed it (launch_sort_small)
+            ev = rank[i];
+        } else {                                             // lower bound; the key is present
+            unsigned long long lo = 0, hi = n_unique;
+            while (lo < hi) {
+                unsigned long long mid = (lo + hi) >> 1;
+                if (uniq[mid] < key) lo = mid + 1; else hi = mid;
+            }
+            ev = lo;
         }
-        const unsigned long long ev = lo;
         if (ev >= n_unique || uniq[ev] != key) continue;
         const uint32_t pat = (uint32_t)(key & ((1u << kPatternBits) - 1u));
         const PatternDesc pd = pds[pat];
@@ -1544,12 +1639,11 @@ __global__ void __launch_bounds__(256) k_line_starts(const uint8_t *__restrict__
     }
 }
 
-template <int BITS>
-cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, const uint4 *bitmap2, uint32_t bits2,
-                             uint32_t *tile_nl, unsigned long long *cand,
-                             unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
-    size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(1u << bits2) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
-    cudaError_t e;
+template <int BITS, bool FOLD>
+cudaError_t launch_scan_one(const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, const uint4 *bitmap2, uint32_t bits2, uint32_t *tile_nl,
+                            unsigned long long *cand, unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    // shared memory: the two bitmaps and the per-warp candidate queues
+    const size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(1u << bits2) / 8 + (size_t)(kScanThreads / 32) * kQueue * 8;
     ScanConsts kc;
     kc.c_nl = 0x0A0A0A0Au;
     kc.c_7f = 0x7F7F7F7Fu;
@@ -1561,16 +1655,17 @@ cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long 
     kc.idx_mul = 1u << (BITS - 5);
     kc.mult = kFilterMult0;
     kc.bm_base = 0;
-    if (fold) {
-        e = cudaFuncSetAttribute(k_scan<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        k_scan<BITS, true><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, kc);
-    } else {
-        e = cudaFuncSetAttribute(k_scan<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        k_scan<BITS, false><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, kc);
-    }
+    cudaError_t e = cudaFuncSetAttribute(k_scan<BITS, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_scan<BITS, FOLD><<<num_sms, kScanThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, kc);
     return cudaGetLastError();
+}
+
+template <int BITS>
+cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, const uint4 *bitmap2, uint32_t bits2,
+                             uint32_t *tile_nl, unsigned long long *cand, unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    return fold ? launch_scan_one<BITS, true>(text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s)
+                : launch_scan_one<BITS, false>(text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
 }
 
 }  // namespace
@@ -1590,13 +1685,14 @@ cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const D
     }
     const uint4 *bitmap = reinterpret_cast<const uint4 *>(fv.bitmap), *bitmap2 = reinterpret_cast<const uint4 *>(fv.bitmap2);
     const uint32_t bits2 = fv.log2_bits2;
+    const bool fold = fv.fold != 0;
     switch (fv.log2_bits) {
-        case 15: return launch_scan_bits<15>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 16: return launch_scan_bits<16>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 17: return launch_scan_bits<17>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 18: return launch_scan_bits<18>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 19: return launch_scan_bits<19>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
-        case 20: return launch_scan_bits<20>(fv.fold != 0, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 15: return launch_scan_bits<15>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 16: return launch_scan_bits<16>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 17: return launch_scan_bits<17>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 18: return launch_scan_bits<18>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 19: return launch_scan_bits<19>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+        case 20: return launch_scan_bits<20>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
         default: return cudaErrorInvalidValue;
     }
 }
@@ -1605,7 +1701,6 @@ cudaError_t launch_prefix(const uint32_t *tile_nl, unsigned long long *tile_pref
     unsigned long long n_blocks = (n_tiles + kPrefBlock - 1) / kPrefBlock;
     if (n_blocks == 0) return cudaSuccess;
     k_prefix_partial<<<(unsigned)n_blocks, kPrefThreads, 0, s>>>(tile_nl, n_tiles, scratch);
-    k_prefix_blocks<<<1, kPrefThreads, 0, s>>>(scratch, n_blocks);
     k_prefix_final<<<(unsigned)n_blocks, kPrefThreads, 0, s>>>(tile_nl, n_tiles, scratch, tile_prefix);
     return cudaGetLastError();
 }
@@ -1621,8 +1716,17 @@ cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, 
                            unsigned long long cand_cap, unsigned long long *tasks, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr,
                            int num_sms, cudaStream_t s) {
     if (lib.fv.log2_bits == 0) return cudaSuccess;
-    k_confirm<<<num_sms * 8, 256, 0, s>>>(text, total_bytes, lib.blob, lib.h, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
-    k_verify<<<num_sms * 16, kVerifyWarps * 32, 0, s>>>(text, total_bytes, lib.blob, lib.h, pt, tasks, raw_cap, raw, raw_cap, ctr);
+    k_confirm<<<num_sms * 8, 256, 0, s>>>(text, total_bytes, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
+    stage_mark("k_confirm");
+    // per-warp shared-memory budget for the task's table: the largest verify table of the library, as long as
+    // 12 CTAs still fit an SM (the register limit of this kernel); larger tables are walked through L1
+    const uint32_t table_cap = lib.verify_table_cap;
+    const size_t vsm = (size_t)kVerifyWarps * table_cap;
+    if (vsm > 40 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsm);
+        if (e != cudaSuccess) return e;
+    }
+    k_verify<<<num_sms * 16, kVerifyWarps * 32, vsm, s>>>(text, total_bytes, lib.blob, lib.h, pt, tasks, raw_cap, raw, raw_cap, ctr, table_cap);
     return cudaGetLastError();
 }
 
@@ -1678,7 +1782,7 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
                            const unsigned long long *keys, const unsigned long long *n_keys_dev, unsigned long long key_cap,
                            const unsigned long long *uniq, const unsigned long long *n_unique_dev, unsigned long long ev_cap, EventOut out,
                            const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side, cudaEvent_t fork_ev, cudaEvent_t join_ev,
-                           cudaEvent_t uniq_ready) {
+                           cudaEvent_t uniq_ready, const uint32_t *rank) {
     if (ev_cap == 0 || key_cap == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(rs.ctr, 0, sizeof(ResolveCounters), s);
     if (e != cudaSuccess) return e;
@@ -1693,7 +1797,10 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     }
     k_plan<<<blocks, kPlanWarps * 32, plan_smem, s>>>(text, lib.blob, lib.h, tile_prefix, pt, keys, n_keys_dev, key_cap, items, rs.item_cap,
                                                       rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots);
-    // short and long lines are independent: walk them concurrently when a side stream is given
+    stage_mark("k_plan");
+    // short and long lines are independent: walk them concurrently when a side stream is given.  (Both in one
+    // launch, the long lines on warp_walk_line in the first CTAs of the grid, was measured in round 2: 47 us
+    // against 26 + 12 us for this pair.)
     const bool fork = side && fork_ev && join_ev;
     if (fork) {
         cudaEventRecord(fork_ev, s);
@@ -1702,14 +1809,17 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     k_check_long<<<num_sms * 16, 128, 0, fork ? side : s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
     if (fork) cudaEventRecord(join_ev, side);
     k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
+    stage_mark("k_check");
     if (fork) cudaStreamWaitEvent(s, join_ev, 0);
+    stage_mark("join k_check_long");
     if (uniq_ready) cudaStreamWaitEvent(s, uniq_ready, 0);   // the sort ran beside plan/check
+    stage_mark("join sort");
     // few, full CTAs: with several batches in flight every SM a small kernel sits on is an SM the next
     // batch's scan CTA (a whole SM each) has to wait for
     unsigned fb = (unsigned)((key_cap + 511) / 512);
     if (fb > (unsigned)num_sms * 2u) fb = (unsigned)num_sms * 2u;
     k_finalize<<<fb, 512, 0, s>>>(lib.blob, lib.h, keys, n_keys_dev, uniq, n_unique_dev, ev_cap, out, items, rs.results,
-                                  reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr);
+                                  reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr, uniq_ready ? rank : nullptr);
     return cudaGetLastError();
 }
 
@@ -1748,7 +1858,8 @@ __global__ void __launch_bounds__(256) k_export(EventOut src, EventOut dst, cons
 cudaError_t launch_export(EventOut src, EventOut dst_host, const unsigned long long *n_rows_dev, unsigned long long cap, const void *ctr_dev, void *ctr_host,
                           size_t ctr_bytes, int num_sms, cudaStream_t s) {
     // a handful of CTAs saturates the PCIe link; more would only sit on SMs that other batches' scans wait for
-    unsigned blocks = (unsigned)std::min<unsigned long long>(8ull, (cap * 64 / 16 + 255) / 256 + 1);
+    static const unsigned max_blocks = getenv("PM_EXPORT_CTAS") ? (unsigned)atoi(getenv("PM_EXPORT_CTAS")) : 8u;
+    unsigned blocks = (unsigned)std::min<unsigned long long>(max_blocks, (cap * 64 / 16 + 255) / 256 + 1);
     (void)num_sms;
     k_export<<<blocks, 256, 0, s>>>(src, dst_host, n_rows_dev, cap, reinterpret_cast<const uint4 *>(ctr_dev), reinterpret_cast<uint4 *>(ctr_host),
                                     (int)((ctr_bytes + 15) / 16));
@@ -1763,6 +1874,7 @@ cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters 
     if (e != cudaSuccess) return e;
     k_sort_merge<<<kSmallSort / 1024, 1024, kSmallSort * 8, s>>>(chunks, ctr, raw_cap, sorted);
     k_sort_unique<<<1, 1024, 0, s>>>(sorted, ctr, raw_cap, uniq, n_unique, big_flag);
+    k_rank<<<kSmallSort / 256, 256, 0, s>>>(raw, ctr, raw_cap, uniq, n_unique, reinterpret_cast<uint32_t *>(chunks));   // the chunk area is free again
     return cudaGetLastError();
 }
 

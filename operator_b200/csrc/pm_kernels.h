@@ -17,6 +17,14 @@
 
 namespace pm {
 
+// PM_DEBUG_TIMING: the runtime points this at a function that records a named CUDA event on the
+// batch's main stream; the multi-kernel launch wrappers call it between their kernels.
+extern thread_local void (*g_stage_mark)(void *arg, const char *name);
+extern thread_local void *g_stage_mark_arg;
+inline void stage_mark(const char *name) {
+    if (g_stage_mark) g_stage_mark(g_stage_mark_arg, name);
+}
+
 constexpr int kTileBytes = 2048;        // one warp iteration of k_scan: 4 x (32 lanes x 16 B)
 constexpr int kScanThreads = 1024;      // one persistent CTA per SM
 constexpr int kHeaderBytes = 16;
@@ -36,6 +44,7 @@ struct DeviceLibrary {
     const uint8_t *blob = nullptr;      // device copy of the compiled blob
     FilterView fv;
     int ctx_slots = 0;                  // newline slots k_plan needs per direction (largest window of the library + 2)
+    uint32_t verify_table_cap = 0;      // bytes of shared memory k_verify gives each warp for its task's table (0: walk through L1)
     BlobHeader h;                       // host copy of the blob header
 };
 
@@ -113,17 +122,18 @@ size_t resolve_aux_bytes();
 // keys[0, *n_keys_dev) is what gets planned and checked (rs.aux holds key_cap entries): either uniq itself,
 // or the raw event queue while the sort that produces uniq is still running on another stream -
 // then uniq_ready is the event recorded after that sort, waited for just before k_finalize, which
-// places each key's row at its rank in uniq[0, *n_unique_dev).  All counts are read on the device;
+// places each key's row at its rank in uniq[0, *n_unique_dev) (rank: the ranks launch_sort_small left in its scratch).  All counts are read on the device;
 // *n_keys_dev > key_cap or *n_unique_dev > ev_cap sets rs.ctr->overflow.
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
                            const unsigned long long *keys, const unsigned long long *n_keys_dev, unsigned long long key_cap,
                            const unsigned long long *uniq, const unsigned long long *n_unique_dev, unsigned long long ev_cap, EventOut out,
                            const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side = nullptr, cudaEvent_t fork_ev = nullptr,
-                           cudaEvent_t join_ev = nullptr, cudaEvent_t uniq_ready = nullptr);
+                           cudaEvent_t join_ev = nullptr, cudaEvent_t uniq_ready = nullptr, const uint32_t *rank = nullptr);
 // Ordering + de-duplication without host involvement for ctr->n_raw <= kSmallSort (otherwise *big_flag = 1 and
 // the caller falls back to launch_sort_unique once it knows the count).
 constexpr int kSmallSort = 16384;
-// Three launches; `scratch` holds 2 * kSmallSort u64.
+// Four launches; `scratch` holds 2 * kSmallSort u64.  Afterwards the first kSmallSort u32 of `scratch` hold, for every raw key,
+// its rank in uniq (what k_finalize needs to place the key's row).
 cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
                               unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s);
 // Gram profile: counts, for every aligned word of text[0, sample_bytes), the occurrences of the

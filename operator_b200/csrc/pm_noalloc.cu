@@ -42,18 +42,53 @@ __device__ __forceinline__ NaHeader *na_header(unsigned char *s) { return reinte
 __device__ __forceinline__ unsigned *na_tile_nl(unsigned char *s) { return reinterpret_cast<unsigned *>(s + kNaHeader); }
 __device__ __forceinline__ unsigned *na_tile_prefix(unsigned char *s) { return reinterpret_cast<unsigned *>(s + kNaHeader + (size_t)kNaMaxTiles * 4); }
 
-// Step 1 (one warp): strip trailing separators the way Java's split does (SPEC.md section 2) and
+// Step 1 (one CTA): strip trailing separators the way Java's split does (SPEC.md section 2) and
 // reset the header.  The previous call's header is still in the scratch, so everything that
 // must start from a known value is written here, not assumed.
-__global__ void k_na_begin(const unsigned char *__restrict__ text, unsigned long long n, unsigned char *scratch) {
-    unsigned long long e = n;
-    if (threadIdx.x == 0) {
-        while (e > 0 && text[e - 1] == '\n') {
-            e--;
-            if (e > 0 && text[e - 1] == '\r') e--;
+//
+// Java drops trailing empty lines, i.e. a suffix of the form ("\r"? "\n")*.  Read backwards that
+// is: the effective end sits just behind the LAST byte that is kept, and a byte is kept when it is
+// neither '\r' nor '\n', or when it is a '\r' that is not directly followed by '\n' (a lone '\r'
+// is text, not a separator).  The CTA searches for that byte from the end, 4 KiB per step, so a
+// log that ends in megabytes of blank lines costs microseconds per megabyte instead of one
+// dependent byte load per separator.
+constexpr int kNaBeginThreads = 1024, kNaBeginPer = 4;
+
+__global__ void __launch_bounds__(kNaBeginThreads) k_na_begin(const unsigned char *__restrict__ text, unsigned long long n, unsigned char *scratch) {
+    __shared__ long long warp_best[kNaBeginThreads / 32];
+    __shared__ long long found_s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr unsigned long long kStep = (unsigned long long)kNaBeginThreads * kNaBeginPer;
+    long long found = -1;
+    for (unsigned long long hi = n; hi > 0 && found < 0; hi = hi > kStep ? hi - kStep : 0) {
+        const unsigned long long lo = hi > kStep ? hi - kStep : 0;
+        long long best = -1;
+#pragma unroll
+        for (int k = 0; k < kNaBeginPer; k++) {
+            const unsigned long long i = lo + (unsigned long long)threadIdx.x * kNaBeginPer + k;
+            if (i < hi) {
+                const unsigned char c = text[i];
+                const bool keep = (c != '\r' && c != '\n') || (c == '\r' && (i + 1 == n || text[i + 1] != '\n'));
+                if (keep) best = (long long)i;
+            }
         }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+        if (lane == 0) warp_best[warp] = best;
+        __syncthreads();
+        if (warp == 0) {
+            long long b2 = warp_best[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) b2 = max(b2, __shfl_xor_sync(0xFFFFFFFFu, b2, o));
+            if (lane == 0) found_s = b2;
+        }
+        __syncthreads();
+        found = found_s;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
         NaHeader *h = na_header(scratch);
-        h->eff_end = e;
+        h->eff_end = (unsigned long long)(found + 1);
         h->n_lines = 0;
     }
 }
@@ -158,6 +193,9 @@ int na_fail(int status, const char *fmt, ...) {
 
 // Device address of the scratch, per device.  The symbol's name is only a host-side stand-in:
 // handing `g_na_scratch` itself to a kernel from host code would pass a host address.
+// The address is looked up once per device ordinal and kept for the life of the process; a
+// cudaDeviceReset() unloads the module it points into, so after a reset this entry point must not be
+// used again in the same process (documented at the declaration).
 constexpr int kNaMaxDevices = 64;
 std::mutex g_na_mu;
 unsigned char *g_na_ptr[kNaMaxDevices] = {nullptr};
@@ -194,14 +232,19 @@ extern "C" int pm_line_index_noalloc(const uint8_t *d_text, uint64_t n_bytes, in
     int rc = na_scratch_for_current_device(&scratch);
     if (rc) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // An error left behind by some earlier, unrelated call on this thread must neither be reported as a
+    // failure of these launches nor be cleared by them: look without clearing, and refuse to launch on top of it.
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess)
+        return na_fail(PM_E_CUDA, "pm_line_index_noalloc: an earlier CUDA error is pending on this thread (%s); nothing was launched", cudaGetErrorString(e));
     const unsigned n_tiles = (unsigned)((n_bytes + kNaTile - 1) / kNaTile);
     const unsigned blocks = n_tiles ? (n_tiles + 7) / 8 : 1;
-    k_na_begin<<<1, 32, 0, s>>>(d_text, n_bytes, scratch);
+    k_na_begin<<<1, kNaBeginThreads, 0, s>>>(d_text, n_bytes, scratch);
     k_na_count<<<blocks < 1184 ? blocks : 1184, 256, 0, s>>>(d_text, scratch);
     k_na_prefix<<<1, 1024, 0, s>>>(scratch, n_bytes);
     k_na_scatter<<<blocks < 1184 ? blocks : 1184, 256, 0, s>>>(d_text, scratch, reinterpret_cast<long long *>(d_line_start), cap,
                                                                  reinterpret_cast<unsigned long long *>(d_n_lines));
-    cudaError_t e = cudaGetLastError();
+    e = cudaGetLastError();   // no error was pending before the four launches above: this one is theirs
     if (e != cudaSuccess) return na_fail(PM_E_CUDA, "pm_line_index_noalloc launch: %s", cudaGetErrorString(e));
     return PM_OK;
 }

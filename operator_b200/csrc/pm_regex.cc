@@ -78,6 +78,7 @@ class Parser {
 
     NodePtr run() {
         decode();
+        unquote();
         if (cps_.empty()) fail(PM_E_UNSUPPORTED, 0, "empty regex");
         Flags fl;
         NodePtr n = alt(fl);
@@ -120,6 +121,66 @@ class Parser {
             offs_.push_back((int)i);
             i += len;
         }
+    }
+
+    // java.util.regex.Pattern rewrites the pattern text before parsing it (Pattern.RemoveQEQuoting;
+    // "Quotation" in the Pattern Javadoc): from the first \Q on, quoted characters are replaced IN
+    // PLACE by individually escaped ones.  So a quantifier after \E binds to the last quoted
+    // character only (`\Qab\E?c` is `ab?c`, `\Qab\E{2}` is `abb`) and quoting also works inside a
+    // character class.  ASCII letters are copied as they are, a digit that opens a quotation becomes
+    // \x3N (it must not extend an escape in front of it), any other ASCII character gets a backslash.
+    // offs_ keeps pointing at the source bytes, so error offsets are unchanged.
+    void unquote() {
+        const size_t n = cps_.size();
+        size_t i = 0;
+        while (i + 1 < n) {
+            if (cps_[i] != '\\')
+                i += 1;
+            else if (cps_[i + 1] != 'Q')
+                i += 2;
+            else
+                break;
+        }
+        if (i + 1 >= n) return;
+        std::vector<uint32_t> out(cps_.begin(), cps_.begin() + i);
+        std::vector<int> origin(offs_.begin(), offs_.begin() + i);
+        auto put = [&](uint32_t c, size_t src) {
+            out.push_back(c);
+            origin.push_back(offs_[src]);
+        };
+        i += 2;
+        bool in_quote = true, begin = true;
+        while (i < n) {
+            const size_t src = i;
+            const uint32_t c = cps_[i++];
+            if (c >= 128 || isalpha_ascii(c)) {
+                put(c, src);
+            } else if (isdig(c)) {
+                if (begin) put('\\', src), put('x', src), put('3', src);
+                put(c, src);
+            } else if (c != '\\') {
+                if (in_quote) put('\\', src);
+                put(c, src);
+            } else if (in_quote) {
+                if (i < n && cps_[i] == 'E') {
+                    i++;
+                    in_quote = false;
+                } else {
+                    put('\\', src), put('\\', src);
+                }
+            } else {
+                if (i < n && cps_[i] == 'Q') {
+                    i++;
+                    in_quote = begin = true;
+                    continue;
+                }
+                put(c, src);
+                if (i < n) put(cps_[i], i), i++;
+            }
+            begin = false;
+        }
+        cps_.swap(out);
+        offs_.swap(origin);
     }
 
     static NodePtr mk(NodeKind k, int pos) {
@@ -402,20 +463,6 @@ class Parser {
                 bool neg;
                 auto r = posix(at, neg);
                 return set(r, fl, at, neg);
-            }
-            case 'Q': {
-                i_++;
-                std::vector<NodePtr> kids;
-                while (!eof() && !(is('\\') && is('E', 1))) {
-                    kids.push_back(lit(peek(), fl, at));
-                    i_++;
-                }
-                if (!eof()) i_ += 2;
-                if (kids.empty()) return mk(NodeKind::Empty, at);
-                if (kids.size() == 1) return std::move(kids[0]);
-                NodePtr n = mk(NodeKind::Cat, at);
-                n->kids = std::move(kids);
-                return n;
             }
             case 'b':
                 i_++;

@@ -119,12 +119,12 @@ struct Device {
     // sixteen events costs more host time than a 1 MB request spends on the GPU.
     struct StreamSet {
         cudaStream_t stream = nullptr, stream2 = nullptr, stream3 = nullptr, scan_stream = nullptr;
-        cudaEvent_t scan_fork = nullptr, scan_join = nullptr, fork_ev[3] = {nullptr, nullptr, nullptr}, join_ev[3] = {nullptr, nullptr, nullptr};
+        cudaEvent_t scan_fork = nullptr, scan_join = nullptr, pods_copied = nullptr, fork_ev[3] = {nullptr, nullptr, nullptr}, join_ev[3] = {nullptr, nullptr, nullptr};
         cudaEvent_t e[10] = {nullptr};
         void destroy() {
             for (cudaStream_t *st : {&stream, &stream2, &stream3, &scan_stream})
                 if (*st) cudaStreamDestroy(*st), *st = nullptr;
-            for (cudaEvent_t *ev : {&scan_fork, &scan_join})
+            for (cudaEvent_t *ev : {&scan_fork, &scan_join, &pods_copied})
                 if (*ev) cudaEventDestroy(*ev), *ev = nullptr;
             for (int k = 0; k < 3; k++) {
                 if (fork_ev[k]) cudaEventDestroy(fork_ev[k]), fork_ev[k] = nullptr;
@@ -263,7 +263,7 @@ struct DevWork {
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
     cudaStream_t stream = nullptr, stream2 = nullptr, stream3 = nullptr;   // 2, 3: work that is independent of the main chain
     cudaStream_t scan_stream = nullptr;   // pipelined mode: k_scan runs in the scan partition of the device
-    cudaEvent_t scan_fork = nullptr, scan_join = nullptr;
+    cudaEvent_t scan_fork = nullptr, scan_join = nullptr, pods_copied = nullptr;
     int sms_scan = 0, sms_post = 0;       // SMs the scan / everything else is sized for
     DeviceLibrary dl;                     // the library view this scan runs with (copied under adapt_mu)
     cudaEvent_t fork_ev[3] = {nullptr, nullptr, nullptr}, join_ev[3] = {nullptr, nullptr, nullptr};
@@ -281,6 +281,11 @@ struct DevWork {
         cudaEventCreate(&ev);
         cudaEventRecord(ev, stream);
         marks.emplace_back(name, ev);
+    }
+    static void mark_hook(void *self, const char *name) { reinterpret_cast<DevWork *>(self)->mark(name); }
+    void hook_marks() {   // lets the multi-kernel launch wrappers of pm_kernels.cu mark their stages as well
+        g_stage_mark = mark_hook;
+        g_stage_mark_arg = this;
     }
 };
 
@@ -346,11 +351,11 @@ void release_work(pm_batch *b) {
                 if (st) cudaStreamSynchronize(st);
             Device::StreamSet ss;
             ss.stream = w.stream, ss.stream2 = w.stream2, ss.stream3 = w.stream3, ss.scan_stream = w.scan_stream;
-            ss.scan_fork = w.scan_fork, ss.scan_join = w.scan_join;
+            ss.scan_fork = w.scan_fork, ss.scan_join = w.scan_join, ss.pods_copied = w.pods_copied;
             for (int k = 0; k < 3; k++) ss.fork_ev[k] = w.fork_ev[k], ss.join_ev[k] = w.join_ev[k];
             for (int k = 0; k < 10; k++) ss.e[k] = w.e[k];
             w.stream = w.stream2 = w.stream3 = w.scan_stream = nullptr;
-            w.scan_fork = w.scan_join = nullptr;
+            w.scan_fork = w.scan_join = w.pods_copied = nullptr;
             for (int k = 0; k < 3; k++) w.fork_ev[k] = w.join_ev[k] = nullptr;
             for (auto &ev : w.e) ev = nullptr;
             bool keep = false;
@@ -399,7 +404,7 @@ struct SoaLayout {
     }
 };
 
-int stage(pm_batch *b) {
+int stage_impl(pm_batch *b) {
     pm_ctx *ctx = b->ctx;
     if (b->staged) return PM_OK;
     {
@@ -454,15 +459,20 @@ int stage(pm_batch *b) {
         b->units[i].dev = best;
         load[best] += b->units[i].len + 64;
     }
+    // Work entries in ascending device order, whatever the pods' order: the loop below takes one
+    // in-flight slot per device and holds it while it waits for the next, so two threads staging
+    // multi-device batches must ask for the devices in the same order or they can deadlock.
     b->work.clear();
     std::vector<int> slot_of(nd, -1);
-    for (size_t i = 0; i < b->units.size(); i++) {
-        int d = b->units[i].dev;
-        if (slot_of[d] < 0) {
+    for (size_t i = 0; i < b->units.size(); i++) slot_of[b->units[i].dev] = 0;
+    for (int d = 0; d < nd; d++)
+        if (slot_of[d] == 0) {
             slot_of[d] = (int)b->work.size();
             b->work.emplace_back();
             b->work.back().slot = d;
         }
+    for (size_t i = 0; i < b->units.size(); i++) {
+        int d = b->units[i].dev;
         DevWork &w = b->work[slot_of[d]];
         b->units[i].local = (int)w.pods.size();
         w.pods.push_back((int)i);
@@ -480,7 +490,7 @@ int stage(pm_batch *b) {
                 Device::StreamSet ss = d->idle_sets.back();
                 d->idle_sets.pop_back();
                 w.stream = ss.stream, w.stream2 = ss.stream2, w.stream3 = ss.stream3, w.scan_stream = ss.scan_stream;
-                w.scan_fork = ss.scan_fork, w.scan_join = ss.scan_join;
+                w.scan_fork = ss.scan_fork, w.scan_join = ss.scan_join, w.pods_copied = ss.pods_copied;
                 for (int k = 0; k < 3; k++) w.fork_ev[k] = ss.fork_ev[k], w.join_ev[k] = ss.join_ev[k];
                 for (int k = 0; k < 10; k++) w.e[k] = ss.e[k];
                 reused = true;
@@ -521,6 +531,7 @@ int stage(pm_batch *b) {
                 CU(cudaStreamCreateWithFlags(&w.stream3, cudaStreamNonBlocking));
                 w.sms_scan = w.sms_post = d->num_sms;
             }
+            CU(cudaEventCreateWithFlags(&w.pods_copied, cudaEventDisableTiming));
             for (int k = 0; k < 3; k++) {
                 CU(cudaEventCreateWithFlags(&w.fork_ev[k], cudaEventDisableTiming));
                 CU(cudaEventCreateWithFlags(&w.join_ev[k], cudaEventDisableTiming));
@@ -576,6 +587,21 @@ int stage(pm_batch *b) {
     }
     b->staged = true;
     return PM_OK;
+}
+
+// A staging that fails half-way (pool out of memory, stream creation) gives back everything it took:
+// the in-flight slots of the devices it had already acquired, their buffers and streams, and its
+// reference to the library - otherwise a retry would leak them and, at depth 1, every later batch on
+// those devices would wait for a slot that is never released.
+int stage(pm_batch *b) {
+    const int rc = stage_impl(b);
+    if (rc != PM_OK && !b->staged) {
+        const std::string msg = g_err;
+        release_work(b);
+        if (b->lib) lib_unref(b->lib), b->lib = nullptr;
+        g_err = msg;
+    }
+    return rc;
 }
 
 // Called with the batch's own streams synchronised.  Other batches may be in flight on the device
@@ -702,6 +728,7 @@ int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
 // from_raw: plan and check the raw queue while the sort is still running on stream3 (join_ev[2]).
 int enqueue_resolve(pm_batch *b, DevWork &w, bool from_raw = false) {
     const DeviceLibrary &dl = w.dl;
+    w.hook_marks();
     SoaLayout L(w.ev_cap);
     ResolveScratch rs{w.rs_items.p, w.item_cap, w.rs_results.as<unsigned char>(), w.rs_long.as<uint32_t>(), w.long_cap, w.rs_aux.p,
                       reinterpret_cast<ResolveCounters *>(w.ctr.as<char>() + kOffResolve)};
@@ -711,9 +738,9 @@ int enqueue_resolve(pm_batch *b, DevWork &w, bool from_raw = false) {
     const uint64_t key_cap = from_raw ? std::min<uint64_t>(w.raw_cap, kSmallSort) : w.ev_cap;
     CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), keys, n_keys, key_cap,
                       w.uniq.as<unsigned long long>(), n_unique, w.ev_cap, L.on(w.ev_soa.p), rs, w.sms_post, w.stream, w.stream2, w.fork_ev[1],
-                      w.join_ev[1], from_raw ? w.join_ev[2] : nullptr));
+                      w.join_ev[1], from_raw ? w.join_ev[2] : nullptr, from_raw ? w.sort_scratch.as<uint32_t>() : nullptr));
     w.launches += 4;
-    w.mark("resolve (plan,check,finalize)");
+    w.mark("k_finalize");
     CU(cudaEventRecord(w.e[6], w.stream));
     // One batch at a time (latency mode): a small kernel writes exactly the rows there are, and the
     // counters, straight into pinned host memory - 26 instead of 35 us at the end of the 1 GiB step,
@@ -747,6 +774,7 @@ int scan_async(pm_batch *b) {
             w.dl = b->lib->dev[w.slot];
         }
         const DeviceLibrary &dl = w.dl;
+        w.hook_marks();
         const int np = (int)w.pods.size();
         // capacity of the result arrays: everything the small sort can deliver on the first scan of a
         // batch, the last event count plus 12 % on a re-scan (less to copy back)
@@ -761,6 +789,8 @@ int scan_async(pm_batch *b) {
             CU(cudaEventRecord(w.scan_fork, w.stream));
             CU(cudaStreamWaitEvent(ss, w.scan_fork, 0));
         }
+        if ((rc = get(d->pool, w.raw_cap * 8, w.tasks))) return rc;
+        if ((rc = get(d->pool, 2 * (size_t)kSmallSort * 8, w.sort_scratch))) return rc;
         CU(cudaEventRecord(w.e[2], ss));
         CU(launch_scan(w.text.as<uint8_t>(), w.n_tiles, dl, w.tile_nl.as<uint32_t>(), w.cand.as<unsigned long long>(), w.cand_cap,
                        w.ctr.as<ScanCounters>(), w.sms_scan, ss));
@@ -775,14 +805,15 @@ int scan_async(pm_batch *b) {
         CU(cudaStreamWaitEvent(w.stream2, w.fork_ev[0], 0));
         CU(launch_prefix(w.tile_nl.as<uint32_t>(), w.tile_prefix.as<unsigned long long>(), w.n_tiles, w.scratch.as<unsigned long long>(), w.stream2));
         CU(launch_pods(w.text.as<uint8_t>(), w.tile_prefix.as<unsigned long long>(), w.pods_dev.as<PodDev>(), np, w.stream2));
-        CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream2));
         CU(cudaEventRecord(w.join_ev[0], w.stream2));
-        if ((rc = get(d->pool, w.raw_cap * 8, w.tasks))) return rc;
-        if ((rc = get(d->pool, 2 * (size_t)kSmallSort * 8, w.sort_scratch))) return rc;
+        // the host's copy of the pod table is only read at gather time: it leaves the device behind the
+        // event k_plan waits for, and the main stream picks it up at the very end (pods_copied)
+        CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream2));
+        CU(cudaEventRecord(w.pods_copied, w.stream2));
         CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.tasks.as<unsigned long long>(),
                           w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), w.sms_post, w.stream));
-        w.launches += 1 + 3 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
-        w.mark("confirm+verify");
+        w.launches += 1 + 2 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
+        w.mark("k_verify");
         CU(cudaEventRecord(w.e[8], w.stream));
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
             const GroupDesc &gd = reinterpret_cast<const GroupDesc *>(b->lib->lib.blob.data() + dl.h.off_groups)[g];
@@ -800,12 +831,13 @@ int scan_async(pm_batch *b) {
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
                              reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream3));
         CU(cudaEventRecord(w.join_ev[2], w.stream3));
-        w.launches += 3;
+        w.launches += 4;
         CU(cudaStreamWaitEvent(w.stream, w.join_ev[0], 0));
         w.mark("join prefix/pods");
         CU(cudaEventRecord(w.e[4], w.stream));
         CU(cudaEventRecord(w.e[5], w.stream));
         if ((rc = enqueue_resolve(b, w, true))) return rc;
+        CU(cudaStreamWaitEvent(w.stream, w.pods_copied, 0));
     }
     return PM_OK;
 }
@@ -1206,10 +1238,25 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
         l->dev.resize(ctx->devs.size());
         l->dev_blobs.assign(ctx->devs.size(), nullptr);
         l->adapt.assign(ctx->devs.size(), AdaptState());
+        // an upload that fails on device d takes the copies on devices 0..d-1 back, so that a second
+        // publish starts from nothing instead of skipping the upload and scanning with null tables
+        auto upload = [&](size_t d) -> cudaError_t {
+            cudaError_t e = cudaSetDevice(ctx->devs[d]->id);
+            if (e == cudaSuccess) e = cudaMalloc(&l->dev_blobs[d], l->lib.blob.size());
+            if (e == cudaSuccess) e = cudaMemcpy(l->dev_blobs[d], l->lib.blob.data(), l->lib.blob.size(), cudaMemcpyHostToDevice);
+            return e;
+        };
         for (size_t d = 0; d < ctx->devs.size(); d++) {
-            CU(cudaSetDevice(ctx->devs[d]->id));
-            CU(cudaMalloc(&l->dev_blobs[d], l->lib.blob.size()));
-            CU(cudaMemcpy(l->dev_blobs[d], l->lib.blob.data(), l->lib.blob.size(), cudaMemcpyHostToDevice));
+            const cudaError_t e = upload(d);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                for (size_t k = 0; k <= d; k++)
+                    if (l->dev_blobs[k]) cudaSetDevice(ctx->devs[k]->id), cudaFree(l->dev_blobs[k]);
+                l->dev.clear();
+                l->dev_blobs.clear();
+                l->adapt.clear();
+                return fail(PM_E_CUDA, "library upload to device %d: %s", ctx->devs[d]->id, cudaGetErrorString(e));
+            }
             l->dev[d].blob = reinterpret_cast<const uint8_t *>(l->dev_blobs[d]);
             l->dev[d].h = *l->lib.header();
             const BlobHeader &bh = *l->lib.header();
@@ -1238,6 +1285,14 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
                 }
                 for (uint32_t i = 0; i < bh.n_secondaries; i++) need = std::max(need, sdv[i].window);
                 l->dev[d].ctx_slots = need + 2;
+                // k_verify copies a task's table into shared memory when it fits the per-warp budget: the largest
+                // table among the filtered primaries, capped so that 4 warps x budget + 3 KiB still lets 11-12 CTAs share an SM
+                const UnitDesc *udv = reinterpret_cast<const UnitDesc *>(hb + bh.off_units);
+                uint32_t cap = 0;
+                for (uint32_t i = 0; i < bh.n_patterns; i++)
+                    if (pdv[i].tier == 1) cap = std::max(cap, (uint32_t)udv[pdv[i].unit].nstates * udv[pdv[i].unit].stride * 2u);
+                static const uint32_t cap_max = getenv("PM_VERIFY_TABLE_CAP") ? (uint32_t)atoi(getenv("PM_VERIFY_TABLE_CAP")) : 4096u;
+                l->dev[d].verify_table_cap = std::min((cap + 255u) & ~255u, cap_max);
             }
         }
     }
@@ -1376,9 +1431,11 @@ int64_t pm_batch_line_index(pm_batch *b, int pod, int64_t *out, int64_t cap) {
 // Accessors for pm_service.cc (same shared object, not part of the C ABI)
 namespace pm {
 std::string &ctx_response_buffer(pm_ctx *ctx) { return ctx->parse_response; }
-pm_library *ctx_current_library(pm_ctx *ctx) {
+bool ctx_current_generation(pm_ctx *ctx, uint64_t *generation) {   // no pointer leaves the lock: a publish may free the library
     std::lock_guard<std::mutex> g(ctx->mu);
-    return ctx->current;
+    if (!ctx->current) return false;
+    *generation = ctx->current->generation;
+    return true;
 }
 const CompiledLibrary &library_compiled(const pm_library *l) { return l->lib; }
 uint64_t library_generation(const pm_library *l) { return l->generation; }

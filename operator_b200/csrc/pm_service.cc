@@ -27,7 +27,7 @@
 #include "podmortem_scan.h"
 
 namespace pm {
-pm_library *ctx_current_library(pm_ctx *ctx);
+bool ctx_current_generation(pm_ctx *ctx, uint64_t *generation);
 const CompiledLibrary &library_compiled(const pm_library *l);
 uint64_t library_generation(const pm_library *l);
 void *ctx_pinned_get(pm_ctx *ctx, size_t bytes, size_t *cap);
@@ -285,14 +285,18 @@ extern "C" int pm_parse(pm_ctx *ctx, const uint8_t *request_json, size_t n, cons
         }
         if (const JsonValue *st = pod->get("status")) collect_finished_at(*st, finished);
     }
-    pm_library *lib = ctx_current_library(ctx);
-    if (!lib) return PM_E_NO_LIBRARY;
-    std::string cache_key;
+    // Only the generation number of the current library is read here, under the context lock: a
+    // concurrent pm_library_publish may drop the last reference to that library at any moment, so no
+    // pointer to it is kept.  The scan below pins the library it actually runs with (job.lib).
+    uint64_t generation = 0;
+    if (!ctx_current_generation(ctx, &generation)) return PM_E_NO_LIBRARY;
+    std::string cache_prefix, cache_tail;
     if (!pod_uid.empty()) {
-        char buf[64];
-        snprintf(buf, sizeof buf, "|%llu|%016llx|%zu", (unsigned long long)library_generation(lib), (unsigned long long)fnv1a(log.data(), log.size()), log.size());
-        cache_key = pod_uid + "|" + finished + buf;
-        if (g_cache.get(cache_key, t_response)) {
+        char buf[48];
+        snprintf(buf, sizeof buf, "|%016llx|%zu", (unsigned long long)fnv1a(log.data(), log.size()), log.size());
+        cache_prefix = pod_uid + "|" + finished + "|";
+        cache_tail = buf;
+        if (g_cache.get(cache_prefix + std::to_string((unsigned long long)generation) + cache_tail, t_response)) {
             *response = t_response.c_str();
             if (response_len) *response_len = t_response.size();
             return PM_OK;
@@ -313,7 +317,7 @@ extern "C" int pm_parse(pm_ctx *ctx, const uint8_t *request_json, size_t n, cons
         set_thread_error(job.err.c_str());
         return job.rc;
     }
-    lib = job.lib;   // the library this request was scanned with (a publish may have happened since)
+    pm_library *lib = job.lib;   // the library this request was scanned with (a publish may have happened since)
     const int64_t n_events = (int64_t)job.pattern.size();
     const CompiledLibrary &cl = library_compiled(lib);
     const PatternDesc *pd = reinterpret_cast<const PatternDesc *>(cl.blob.data() + cl.header()->off_patterns);
@@ -376,7 +380,7 @@ extern "C" int pm_parse(pm_ctx *ctx, const uint8_t *request_json, size_t n, cons
     o += ",\"processingTimeMs\":" + json_number(ms);
     o += ",\"patternsUsed\":" + std::to_string((long long)cl.patterns.size());
     o += ",\"engine\":\"podmortem-scan-b200\"}}";
-    if (!cache_key.empty()) g_cache.put(cache_key, o);
+    if (!cache_prefix.empty()) g_cache.put(cache_prefix + std::to_string((unsigned long long)library_generation(lib)) + cache_tail, o);
     *response = o.c_str();
     if (response_len) *response_len = o.size();
     return PM_OK;

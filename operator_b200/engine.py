@@ -18,7 +18,8 @@ from typing import Dict, Iterable, List, Optional, Sequence, Union
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpodmortem_scan.so")
+# PM_SCAN_LIBRARY: another build of the same library (kernel experiments); the default is the in-tree build
+LIB_PATH = os.environ.get("PM_SCAN_LIBRARY") or os.path.join(_HERE, "libpodmortem_scan.so")
 
 PM_OK = 0
 STATUS = {0: "PM_OK", -1: "PM_E_INVALID", -2: "PM_E_SYNTAX", -3: "PM_E_UNSUPPORTED", -4: "PM_E_TOO_COMPLEX",

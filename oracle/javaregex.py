@@ -103,9 +103,74 @@ class _Flags:
     dotall: bool = False
 
 
+def _remove_qe_quoting(src: str):
+    """java.util.regex.Pattern rewrites the pattern text before it parses it (Pattern.RemoveQEQuoting
+    in the JDK sources; behaviour documented under "Quotation" in the Pattern Javadoc): from the first
+    \\Q on, quoted characters become individually escaped characters IN PLACE.  Consequences the
+    parser must reproduce: a quantifier after \\E binds to the LAST quoted character only
+    (`\\Qab\\E?c` is `ab?c`), quoting works inside a character class, ASCII letters are copied as they
+    are, a digit that opens a quotation becomes \\x3N (so it cannot extend an escape in front of it),
+    every other ASCII character gets a backslash.  Returns the rewritten text and, per character of
+    it, the index of the source character it came from (error offsets refer to the source)."""
+    n = len(src)
+    i = 0
+    while i < n - 1:
+        if src[i] != "\\":
+            i += 1
+        elif src[i + 1] != "Q":
+            i += 2
+        else:
+            break
+    if i >= n - 1:
+        return src, list(range(n))
+    out = list(src[:i])
+    origin = list(range(i))
+    i += 2
+    in_quote, begin = True, True
+
+    def put(ch, at):
+        out.append(ch)
+        origin.append(at)
+
+    while i < n:
+        at = i
+        c = src[i]
+        i += 1
+        if ord(c) >= 128 or (c.isalpha() and c.isascii()):
+            put(c, at)
+        elif c.isdigit() and c.isascii():
+            if begin:
+                for ch in "\\x3":
+                    put(ch, at)
+            put(c, at)
+        elif c != "\\":
+            if in_quote:
+                put("\\", at)
+            put(c, at)
+        elif in_quote:
+            if i < n and src[i] == "E":
+                i += 1
+                in_quote = False
+            else:
+                put("\\", at)
+                put("\\", at)
+        else:
+            if i < n and src[i] == "Q":
+                i += 1
+                in_quote, begin = True, True
+                continue
+            put(c, at)
+            if i < n:
+                put(src[i], i)
+                i += 1
+        begin = False
+    return "".join(out), origin
+
+
 class _Parser:
     def __init__(self, src: str):
-        self.s = src
+        self.src_len = len(src)
+        self.s, self.origin = _remove_qe_quoting(src)
         self.i = 0
 
     # -- helpers
@@ -114,7 +179,8 @@ class _Parser:
         return self.s[j] if j < len(self.s) else ""
 
     def _err(self, kind, msg, at=None):
-        raise JavaRegexError(kind, self.i if at is None else at, msg)
+        at = self.i if at is None else at
+        raise JavaRegexError(kind, self.origin[at] if at < len(self.origin) else self.src_len, msg)
 
     # -- grammar
     def parse(self) -> Node:
@@ -363,15 +429,6 @@ class _Parser:
         if c in "pP":
             r, neg = self._posix(at)
             return self._set(r, fl, at, negate=neg)
-        if c == "Q":
-            self.i += 1
-            j = self.s.find("\\E", self.i)
-            body = self.s[self.i:] if j < 0 else self.s[self.i:j]
-            self.i = len(self.s) if j < 0 else j + 2
-            kids = [self._lit(ord(ch), fl, at) for ch in body]
-            if not kids:
-                return Node("cat", kids=[Node("empty", pos=at)], pos=at)
-            return kids[0] if len(kids) == 1 else Node("cat", kids=kids, pos=at)
         if c == "b":
             self.i += 1
             if self._peek() == "{":

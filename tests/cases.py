@@ -40,6 +40,10 @@ REGEXES = [
     r"été \w+",
     r"(?i)[a-c]{3}-\d",
     r"\P{Alpha}\p{Upper}{3}\P{Alpha}",
+    # \Q..\E is rewritten in place by Java: a quantifier after \E binds to the last quoted character
+    r"^\Qab\E?c$",
+    r"x\Qa.\E{2}y",
+    r"[\Q^-\E]+\d",
 ]
 
 TAB = chr(9)
@@ -57,6 +61,7 @@ LINES = [
     "E123 fatal", "Caused by: java.io.IOException", TAB + "... 12 more", TAB + "... 3 common frames omitted", "  Suppressed: x", "Suppressed: x",
     "xxy", "xxxy", "xxxxxxy", "abcd", "acd", "abd", "ad", "abbcd", "java.lang.NullPointerException", "java.lang.Exception",
     "[]", "][", "[x]", TAB + "com.acme.Foo(Foo.java:10)", "segfault at 7f3a ip 00000000004005d4 sp", "segfault at zz ip 1",
+    "ac", "c", "abc", "xa..y", "xa.a.y", "xa.y", "^-^5", "a5",
     "x" * 300 + " OutOfMemoryError " + "y" * 5000, "é" * 700 + "connection reset", "été chaud", "ete chaud",
     "AbC-7", "abd-7", " OOM ", "xOOMx", "a ", "foo ", "bar",
 ]

@@ -63,6 +63,14 @@ def test_split_known_answers(log, want):
     (r"[^a]", "\r", True),                 # negated classes do match line terminators
     (r"\p{Punct}", "_", True),
     (r"\Qa+b\E", "a+b", True),
+    (r"^\Qab\E?c$", "c", False),          # quotation is rewritten in place: the quantifier binds to 'b' alone
+    (r"^\Qab\E?c$", "ac", True),
+    (r"^\Qab\E{2}$", "abb", True),
+    (r"^\Qab\E{2}$", "abab", False),
+    (r"[\Q^-\E]x", "^x", True),           # ... and it works inside a character class
+    (r"[\Q^-\E]x", "ax", False),
+    (r"a\Q1\E2+", "a122", True),          # a digit that opens a quotation becomes \x31
+    (r"a\Q\E+", "aa", True),              # an empty quotation vanishes: the quantifier binds to 'a'
     (r"a{2}", "aa", True),
     (r"a{2,}?b", "aaab", True),
 ])
