@@ -2,7 +2,7 @@
 #   operator_b200/libpodmortem_scan.so   product: compiler + runtime + sm_100a kernels (C ABI)
 #   tests/support/libpm_testsupport.so   CPU unit-test harness for the pattern compiler
 #   oracle/_build/liboracle_pcre2.so     test oracle / CPU baseline (PCRE2 via dlopen)
-#   operator_b200/libpm_synth.so         synthetic corpus generator (bench + tests input)
+#   operator_b200/libpm_synth.so         synthetic corpus generator, host and device (bench + tests input)
 NVCC ?= /usr/local/cuda/bin/nvcc
 CXX ?= g++
 ARCH := -gencode arch=compute_100a,code=sm_100a
@@ -34,8 +34,8 @@ oracle/_build/liboracle_pcre2.so: oracle/scan_pcre2.c
 	mkdir -p oracle/_build
 	gcc -O2 -fPIC -shared -pthread -o $@ $< -ldl
 
-operator_b200/libpm_synth.so: operator_b200/csrc/synth/pm_synth.cc
-	$(CXX) $(CXXFLAGS) -shared -pthread -o $@ $<
+operator_b200/libpm_synth.so: operator_b200/csrc/synth/pm_synth.cc operator_b200/csrc/synth/pm_synth_gpu.cu operator_b200/csrc/synth/pm_synth_core.h
+	$(NVCC) $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-pthread -shared -o $@ operator_b200/csrc/synth/pm_synth.cc operator_b200/csrc/synth/pm_synth_gpu.cu -lcudart
 
 clean:
 	rm -f $(CSRC)/*.o $(CSRC)/*.log operator_b200/*.so tests/support/*.so oracle/_build/*.so

@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--depth", type=int, default=5, help="batches in flight per GPU in the throughput legs (pm_set_pipeline); 1 = one at a time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--config5-gib", type=int, default=64, help="size of the fixed corpus of the strong-scaling leg (0: skip)")
+    ap.add_argument("--config3-pods-per-gpu", type=int, default=1250, help="pods per GPU of the crash-storm leg (0: skip)")
     ap.add_argument("--ref-budget-s", type=float, default=150.0, help="--impl reference: wall-clock budget for warm-up + timed steps")
     return ap.parse_args()
 
@@ -185,6 +187,304 @@ def run_reference(args, rank, world):
     }))
 
 
+
+# ------------------------------------------------------------------------------------------------
+# BASELINE configs 3 and 5: corpora of 17-64 GB per GPU, generated on the device (the counter-based
+# generator as a kernel, byte-identical to the host generator) and handed over as device pointers.
+
+def device_corpus(torch, target_bytes, wit, swit, p_hit, first_line):
+    from operator_b200 import synth
+    t = torch.empty(target_bytes, dtype=torch.uint8, device="cuda")
+    n, lines = synth.make_corpus_device(t.data_ptr(), target_bytes, wit, swit, p_hit=p_hit, first_line=first_line)
+    return t, n, lines
+
+
+def timed_rescans(b, dist, steps, warmup, sync_all):
+    """Device time of `steps` one-batch-at-a-time scans of a staged batch (CUDA events inside the library)."""
+    for _ in range(warmup):
+        r = b.rescan(copy=False)
+    sync_all()
+    ms = scan = 0.0
+    for _ in range(steps):
+        r = b.rescan(copy=False)
+        ms += r.ms_total
+        scan += r.ms_scan
+    sync_all()
+    return ms / steps, scan / steps, r
+
+
+def leg_config5(args, eng, torch, dist, dev, rank, world, wit, swit, sync_all, peak):
+    """64 GiB corpus, fixed size, split by pod over the ranks: strong scaling (N = 1 holds all of it)."""
+    n_pods, pod_bytes = args.config5_gib, 1 << 30
+    b = eng.batch()
+    my_bytes = my_lines = 0
+    tensors = []
+    for k in range(rank, n_pods, world):
+        t, n, lines = device_corpus(torch, pod_bytes, wit, swit, P_HIT, (1000 + k) << 36)
+        b.add_pod_device(t.data_ptr(), n, k, keep=t)
+        tensors.append(t)
+        my_bytes += n
+        my_lines += lines
+    b.stage()
+    b._keep.clear()
+    del tensors, t
+    torch.cuda.empty_cache()          # the staged copy is what gets scanned
+    steps = max(2, min(args.steps, 5))
+    ms, ms_scan, r = timed_rescans(b, dist, steps, 2, sync_all)
+    events = int(r.n_events)
+    b.release()
+    ms_max = dist.max_over_ranks(ms, dev)
+    scan_max = dist.max_over_ranks(ms_scan, dev)
+    total = dist.sum_over_ranks(my_bytes, dev)
+    all_events = dist.sum_over_ranks(events, dev)
+    gbs = total / (ms_max * 1e-3) / 1e9
+    return {"workload": "configs[4]: %d GiB synthetic corpus (%d pods of 1 GiB, generated on the device), fixed size, pods split over %d GPU(s)" % (n_pods, n_pods, world),
+            "scaling": "strong", "bytes": int(total), "n_gpus": world, "steps": steps, "ms_per_step": ms_max, "k_scan_ms": scan_max,
+            "gbs": gbs, "frac_of_measured_hbm_x_gpus": gbs / (peak * world), "k_scan_gbs": total / (scan_max * 1e-3) / 1e9,
+            "events": int(all_events), "one_batch_at_a_time": True}
+
+
+def leg_config3(args, eng, torch, dist, dev, rank, world, lib_json, wit, swit, sync_all, peak):
+    """Crash storm: 10 000 failed pods x 100 000 lines, pod-sharded over 8 GPUs = 1250 pods per GPU.  With
+    fewer GPUs the pod count shrinks in proportion (1250 x N pods): per-GPU work is the configuration's."""
+    import numpy as np
+    from oracle import pcre2_oracle as po
+    per_gpu = args.config3_pods_per_gpu
+    pod_bytes = 100_000 * 143          # ~100 000 lines of ~143 bytes
+    b = eng.batch()
+    tensors, sizes, lines_of = [], [], []
+    my_bytes = 0
+    for j in range(per_gpu):
+        pod_id = rank * per_gpu + j
+        t, n, lines = device_corpus(torch, pod_bytes, wit, swit, P_HIT, (5000 + pod_id) << 36)
+        b.add_pod_device(t.data_ptr(), n, pod_id, keep=t)
+        tensors.append(t)
+        sizes.append(n)
+        lines_of.append(lines)
+        my_bytes += n
+    b.stage()
+    b._keep.clear()
+    del tensors, t
+    torch.cuda.empty_cache()
+    steps = max(2, min(args.steps, 5))
+    for _ in range(2):
+        r = b.rescan(copy=False)
+    sync_all()
+    ms = scan = 0.0
+    for i in range(steps):
+        r = b.rescan(copy=(i == steps - 1))
+        ms += r.ms_total
+        scan += r.ms_scan
+    sync_all()
+    ms, scan = ms / steps, scan / steps
+    # parity on 64 seeded pods (over all ranks) regenerated on the host: the (line, pattern) pairs of each must equal
+    # the PCRE2 loop's
+    sample = [p for p in np.random.RandomState(3).permutation(per_gpu * world)[:64].tolist() if p // per_gpu == rank]
+    ok, checked, pairs = True, 0, 0
+    plib = po.Pcre2Library([p["primary_pattern"]["regex"] for p in lib_json["patterns"]])
+    for pod_id in sample:
+        from operator_b200 import synth
+        j = pod_id - rank * per_gpu
+        host, host_lines = synth.make_corpus(pod_bytes, wit, swit, p_hit=P_HIT, first_line=(5000 + pod_id) << 36)
+        starts, lens = po.split(host)
+        ol, op, total = po.scan(plib, host, starts, lens, threads=max(1, (os.cpu_count() or 1) // world))
+        want = np.stack([ol.astype(np.int64) + 1, op.astype(np.int64)], axis=1)
+        want = want[np.lexsort((want[:, 1], want[:, 0]))]
+        a, e = int(r.pod_first_event[j]), int(r.pod_first_event[j + 1])
+        got = np.stack([r.line_no[a:e].astype(np.int64), r.pattern_index[a:e].astype(np.int64)], axis=1)
+        ok = ok and int(host.size) == sizes[j] and host_lines == lines_of[j] == int(r.pod_n_lines[j]) and want.shape == got.shape and bool(np.array_equal(want, got))
+        checked += 1
+        pairs += int(want.shape[0])
+    plib.close()
+    events = int(r.n_events)
+    b.release()
+    ms_max = dist.max_over_ranks(ms, dev)
+    scan_max = dist.max_over_ranks(scan, dev)
+    total = dist.sum_over_ranks(my_bytes, dev)
+    gbs = total / (ms_max * 1e-3) / 1e9
+    return {"workload": "configs[2]: crash storm, %d pods x ~100 000 lines (%d per GPU; the configuration is 10 000 pods on 8 GPUs, scaled in proportion "
+                        "to the GPU count), generated on the device, pod-sharded" % (per_gpu * world, per_gpu),
+            "scaling": "weak", "bytes": int(total), "pods": per_gpu * world, "n_gpus": world, "steps": steps, "ms_per_step": ms_max, "k_scan_ms": scan_max,
+            "gbs": gbs, "frac_of_measured_hbm_x_gpus": gbs / (peak * world), "events": int(dist.sum_over_ranks(events, dev)),
+            "parity": {"pods_checked": int(dist.sum_over_ranks(checked, dev)), "pairs": int(dist.sum_over_ranks(pairs, dev)),
+                       "equal": dist.sum_over_ranks(0 if ok else 1, dev) == 0,
+                       "what": "per sampled pod: bytes and line count of the host-regenerated text, and every (line_no, pattern_index) pair vs the PCRE2 loop"}}
+
+
+def measure_corpus(eng, torch, dist, dev_tensor, nbytes, steps, depth, sync_all):
+    """One device-resident corpus: step time one batch at a time (latency) and with `depth` batches in flight
+    (throughput), plus the counters of a step."""
+    b = eng.batch()
+    b.add_pod_device(dev_tensor.data_ptr(), nbytes, 0, keep=dev_tensor)
+    b.stage()
+    ms, ms_scan, r = timed_rescans(b, dist, steps, 4, sync_all)
+    one = {"ms_per_step": ms, "k_scan_ms": ms_scan, "post_ms": float(r.ms_post), "dfa_ms": float(r.ms_dfa), "gbs": nbytes / (ms * 1e-3) / 1e9}
+    stats = {"filter_candidates": int(r.n_candidates), "literal_confirms": int(r.n_verified), "events": int(r.n_events)}
+    want = int(r.n_events)
+    b.release()
+    piped = None
+    if depth > 1:
+        eng.set_pipeline(depth, 0)
+        batches = []
+        for _ in range(depth):
+            bb = eng.batch()
+            bb.add_pod_device(dev_tensor.data_ptr(), nbytes, 0, keep=dev_tensor)
+            bb.stage()
+            batches.append(bb)
+
+        def run(n):
+            ok = True
+            for bb in batches[:min(depth, n)]:
+                bb.submit()
+            for i in range(n):
+                rr = batches[i % depth].wait(copy=False)
+                ok = ok and int(rr.n_events) == want
+                if i + depth < n:
+                    batches[i % depth].submit()
+            return ok
+
+        run(2 * depth)
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_timed = max(2 * depth, steps)
+        e0.record()
+        ok = run(n_timed)
+        e1.record()
+        sync_all()
+        ms_p = e0.elapsed_time(e1) / n_timed
+        piped = {"batches_in_flight": depth, "ms_per_step": ms_p, "gbs": nbytes / (ms_p * 1e-3) / 1e9, "same_events_every_step": ok}
+        for bb in batches:
+            bb.release()
+        eng.set_pipeline(1, 0)
+    return one, piped, stats
+
+
+def leg_hit_sweep(args, eng, torch, dist, lib_json, wit, swit, sync_all, peak):
+    """Hit density and near-miss lines: p_hit in {0, 1e-4, 1e-3, 1e-2}; in every corpus 1e-3 of the lines
+    are near misses (a witness with its head or tail cut off: library vocabulary, often the required literal, no match)."""
+    from operator_b200 import synth
+    near = synth.near_misses(wit)
+    eng.compile_library(lib_json).publish()
+    out = []
+    for p_hit in (0.0, 1e-4, 1e-3, 1e-2):
+        t = torch.empty(args.corpus_bytes, dtype=torch.uint8, device="cuda")
+        n, lines = synth.make_corpus_device(t.data_ptr(), args.corpus_bytes, wit, swit, p_hit=p_hit, first_line=77 << 36, p_near=1e-3, near=near)
+        one, piped, stats = measure_corpus(eng, torch, dist, t, n, max(3, min(args.steps, 10)), args.depth, sync_all)
+        row = {"p_hit": p_hit, "p_near": 1e-3, "lines": lines}
+        row.update(stats)
+        row["one_batch_at_a_time"] = one
+        row["pipelined"] = piped
+        row["frac_of_measured_hbm"] = (piped or one)["gbs"] / peak
+        out.append(row)
+        del t
+        torch.cuda.empty_cache()
+    return out
+
+
+def leg_mixed_library(args, eng, torch, dist, sync_all, peak):
+    """The 500-pattern library with every tenth primary replaced by a short-literal / class-led regex
+    (\\bOOM\\b, exit code 137\\b, (?i)errno \\d+, [Cc]ache (evicted|flushed), ...): what has no 7-byte literal goes to
+    the combined shared-memory DFA (k_dfa_scan), a second pass over the text."""
+    from operator_b200 import synth
+    lj, w, sw = synth.make_mixed_library(args.patterns)
+    rep = eng.compile_library(lj).publish().report
+    t = torch.empty(args.corpus_bytes, dtype=torch.uint8, device="cuda")
+    n, lines = synth.make_corpus_device(t.data_ptr(), args.corpus_bytes, w, sw, p_hit=P_HIT, first_line=78 << 36)
+    one, piped, stats = measure_corpus(eng, torch, dist, t, n, max(3, min(args.steps, 10)), args.depth, sync_all)
+    del t
+    torch.cuda.empty_cache()
+    groups = max(1, rep["dfa_groups"])
+    row = {"workload": "config-2 corpus vs the mixed 500-pattern library (10 % short-literal / class-led primaries)",
+           "library": {k: rep[k] for k in ("n_patterns", "n_filtered", "n_dfa_scanned", "dfa_groups", "dfa_states", "dfa_classes", "blob_bytes")},
+           "k_dfa_scan_gbs_per_pass": n / (one["dfa_ms"] / groups * 1e-3) / 1e9 if one["dfa_ms"] > 0 else None,
+           "k_dfa_scan_frac_of_measured_hbm": (n / (one["dfa_ms"] / groups * 1e-3) / 1e9 / peak) if one["dfa_ms"] > 0 else None}
+    row.update(stats)
+    row["one_batch_at_a_time"] = one
+    row["pipelined"] = piped
+    row["frac_of_measured_hbm"] = (piped or one)["gbs"] / peak
+    return row
+
+
+def leg_single_context(args, torch, world, local, lib_json, wit, swit, peak):
+    """Rank 0 alone: ONE context over all N GPUs of the node, the way a single /parse service on a multi-GPU box runs
+    (pods placed over the devices, per-device streams, host gather in batch order) - a crash-storm-shaped batch of
+    device-resident pods, checked pod for pod against a one-GPU context; and one host-resident log large enough to be
+    cut across the devices (line-aligned pieces with halos), checked against the uncut scan."""
+    import numpy as np
+    from operator_b200 import Engine, synth
+    pods_per_dev, pod_bytes = 64, 100_000 * 143
+    eng = Engine(devices=list(range(world)))
+    one = Engine(devices=[0])
+    out = {"n_gpus": world}
+    try:
+        eng.compile_library(lib_json).publish()
+        one.compile_library(lib_json).publish()
+        b = eng.batch()
+        total = 0
+        for d in range(world):
+            torch.cuda.set_device(d)
+            for j in range(pods_per_dev):
+                pod_id = d * pods_per_dev + j
+                t, n, _ = device_corpus(torch, pod_bytes, wit, swit, P_HIT, (9000 + pod_id) << 36)
+                b.add_pod_device(t.data_ptr(), n, pod_id, keep=t)
+                total += n
+        b.stage()
+        for _ in range(2):
+            r = b.rescan(copy=False)
+        ms = 0.0
+        t0 = time.perf_counter()
+        for i in range(3):
+            r = b.rescan(copy=(i == 2))
+            ms += r.ms_total
+        wall = (time.perf_counter() - t0) / 3
+        ms /= 3
+
+        def fingerprints(res, n_pods):
+            fp = []
+            for k in range(n_pods):
+                a, e = int(res.pod_first_event[k]), int(res.pod_first_event[k + 1])
+                fp.append((e - a, int(res.line_no[a:e].astype(np.int64).sum()), int(res.pattern_index[a:e].astype(np.int64).sum()),
+                           int(res.ctx_end[a:e].sum()), float(res.score[a:e].sum()), int(res.pod_n_lines[k])))
+            return fp
+
+        got = fingerprints(r, world * pods_per_dev)
+        events = int(r.n_events)
+        b.release()
+        torch.cuda.empty_cache()
+        # the same pods, 64 at a time, on a one-GPU context
+        torch.cuda.set_device(0)
+        same = True
+        for d in range(world):
+            rb = one.batch()
+            for j in range(pods_per_dev):
+                pod_id = d * pods_per_dev + j
+                t, n, _ = device_corpus(torch, pod_bytes, wit, swit, P_HIT, (9000 + pod_id) << 36)
+                rb.add_pod_device(t.data_ptr(), n, pod_id, keep=t)
+            rb.submit()
+            want = fingerprints(rb.wait(), pods_per_dev)
+            rb.release()
+            same = same and want == got[d * pods_per_dev:(d + 1) * pods_per_dev]
+        gbs = total / (ms * 1e-3) / 1e9
+        out["pod_sharded_batch"] = {"pods": world * pods_per_dev, "bytes": total, "events": events, "device_ms_per_step": ms, "host_wall_ms_per_step": wall * 1e3,
+                                    "gbs": gbs, "frac_of_measured_hbm_x_gpus": gbs / (peak * world), "equals_one_gpu_context_pod_for_pod": same}
+        # one large host-resident log, cut across the devices
+        log_bytes = min(world + 1, 9) * (64 << 20)
+        log, lines = synth.make_corpus(log_bytes, wit, swit, p_hit=P_HIT, first_line=9900 << 36)
+        t0 = time.perf_counter()
+        rc = eng.scan([log])
+        wall_cut = time.perf_counter() - t0
+        ru = one.scan([log])
+        equal = rc.n_events == ru.n_events and all(np.array_equal(getattr(rc, f), getattr(ru, f)) for f in
+                                                   ("pattern_index", "line_no", "line_start", "line_len", "ctx_first_line", "ctx_last_line", "ctx_start", "ctx_end", "score", "pod_n_lines"))
+        out["large_log_cut_across_devices"] = {"bytes": int(log.size), "lines": lines, "events": int(rc.n_events), "pieces": min(world, int(log.size) // (64 << 20)),
+                                               "host_wall_ms": wall_cut * 1e3, "equals_uncut_scan": bool(equal)}
+    finally:
+        eng.close()
+        one.close()
+        torch.cuda.set_device(local)
+    return out
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -274,7 +574,7 @@ def main():
                 bb.submit()
         return launches_, ok
 
-    run_steps(max(args.warmup, 3))
+    run_steps(max(args.warmup, 3, depth))   # every batch in flight has been through its first scan
     sync_all()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
@@ -339,6 +639,17 @@ def main():
                           "frac_of_measured_hbm": nbytes / (ms_s / 5 * 1e-3) / 1e9 / peak_hbm()[0], "events": int(sr.n_events),
                           "filter_candidates": int(sr.n_candidates), "library_blob_bytes": rep["blob_bytes"], "compile_s": round(compile_s, 2)})
             sb.release()
+        # config 4 (20 000 patterns): where the post-scan time goes, stage by stage - a child process with the stage marks
+        # switched on (every mark is an event record on the main stream and adds ~2 us, so the marked steps are not the timed ones)
+        try:
+            child = subprocess.run([sys.executable, os.path.join(ROOT, "tools_tail_bench.py"), "--patterns", "20000", "--steps", "3", "--stages"],
+                                   capture_output=True, text=True, timeout=600)
+            last = [l for l in child.stdout.splitlines() if l.startswith("{")][-1]
+            sweep[-1]["post_scan_stages_us"] = json.loads(last)["stages_us"]
+            sweep[-1]["post_scan_stages_note"] = "CUDA events between the kernels of one step, in stream order; ncu L2 hit rates of these kernels: profiles/r02_config4_ncu.md"
+        except Exception as e:   # the detail is a report, not a gate
+            sweep[-1]["post_scan_stages_us"] = None
+            sweep[-1]["post_scan_stages_note"] = "unavailable: %r" % (e,)
         eng.compile_library(lib_json).publish()
 
     # ---- configs[4] shaped (one large device-resident batch: here 8 pods x the 1 GiB corpus): the fixed
@@ -382,6 +693,22 @@ def main():
         small_pinned.free()
         eng.compile_library(lib_json).publish()
 
+    # ---- hit density / near misses, and the mixed library that reaches the combined DFA (N = 1)
+    hit_sweep = mixed = None
+    if world == 1 and not args.no_sweep:
+        hit_sweep = leg_hit_sweep(args, eng, torch, dist, lib_json, wit, swit, sync_all, peak_hbm()[0])
+        mixed = leg_mixed_library(args, eng, torch, dist, sync_all, peak_hbm()[0])
+        eng.compile_library(lib_json).publish()
+
+    # ---- BASELINE configs 3 and 5 (every rank takes part)
+    cfg3 = cfg5 = None
+    if not args.no_sweep:
+        eng.compile_library(lib_json).publish()
+        if args.config5_gib > 0:
+            cfg5 = leg_config5(args, eng, torch, dist, dev, rank, world, wit, swit, sync_all, peak_hbm()[0])
+        if args.config3_pods_per_gpu > 0:
+            cfg3 = leg_config3(args, eng, torch, dist, dev, rank, world, lib_json, wit, swit, sync_all, peak_hbm()[0])
+
     # ---- reductions: max time over ranks, sum of bytes
     step_ms = dist.max_over_ranks(ms_bracket / args.steps, dev)
     serial_ms = dist.max_over_ranks(ms_total / serial_steps, dev)
@@ -390,6 +717,17 @@ def main():
     wall_dev_s = dist.max_over_ranks(wall_dev / args.steps, dev)
     total_bytes = dist.sum_over_ranks(nbytes, dev)
     h2d_ms = dist.max_over_ranks(ms_h2d / e2e_steps, dev)
+
+    # ---- the product's own multi-GPU path: rank 0 alone opens ONE context over all N GPUs (the other ranks have
+    #      closed theirs and wait at the final barrier)
+    single = None
+    if world > 1 and not args.no_sweep:
+        eng.close()
+        eng = None
+        torch.cuda.empty_cache()
+        dist.barrier()
+        if rank == 0:
+            single = leg_single_context(args, torch, world, local, lib_json, wit, swit, peak_hbm()[0])
 
     parity_failed = False
     if rank == 0:
@@ -429,6 +767,11 @@ def main():
             "pattern_sweep": sweep,
             "large_batch": large,
             "config1_latency": latency,
+            "hit_sweep": hit_sweep,
+            "mixed_library": mixed,
+            "config3_crash_storm": cfg3,
+            "config5_fixed_corpus": cfg5,
+            "single_context": single,
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
@@ -446,9 +789,12 @@ def main():
             else:
                 out["parity_check"] = {"pairs": int(n_match), "equal": None, "what": "not comparable: the CPU leg did not cover the whole corpus"}
         print(json.dumps(out))
-    pinned.free()
-    eng.close()
+    if eng is not None:
+        if pinned is not None:
+            pinned.free()
+        eng.close()
     if world > 1:
+        dist.barrier()
         import torch.distributed as td
         td.destroy_process_group()
     if parity_failed:

@@ -30,7 +30,9 @@
 extern "C" {
 #endif
 
-#define PM_ABI_VERSION 2
+/* 2: pm_set_pipeline, pm_parse_stats, pm_library_serialize/load, pm_line_index_noalloc, pm_noalloc_last_error
+ * 3: pm_batch_add_pod_device */
+#define PM_ABI_VERSION 3
 
 typedef enum pm_status {
     PM_OK = 0,
@@ -94,7 +96,7 @@ typedef struct pm_result_view {
      * (max over devices) */
     double ms_h2d, ms_scan, ms_post, ms_d2h;
     /* first kernel of the scan to the results on the host, one CUDA-event pair per device, max over
-     * devices (no host round trip inside unless a queue overflowed or the batch has more than 16384
+     * devices (no host round trip inside unless a queue overflowed or the batch has more than 131072
      * raw events; with several batches in flight it includes waiting for SMs other batches hold) */
     double ms_total;
     /* the combined-DFA kernel(s) alone (0 when the library has no DFA-scanned pattern) */
@@ -155,6 +157,11 @@ int pm_batch_wait(pm_batch *, pm_result_view *out);   /* blocks the calling thre
 void pm_batch_release(pm_batch *);
 
 /* ---- device-resident corpora (benchmarks; the roofline leg of bench.py) ---------------- */
+/* A pod whose bytes already live in device memory on one of the context's GPUs (BASELINE configs 3 and 5:
+ * corpora of 17-64 GB per GPU are generated where they are scanned).  The pod is staged on that GPU with a
+ * device-to-device copy and is never cut across devices; everything else is as for pm_batch_add_pod.  No
+ * counterpart in the reference (its logs arrive over HTTP, PodFailureWatcher.java:319-335). */
+int pm_batch_add_pod_device(pm_batch *, const void *d_log, size_t n, uint64_t pod_tag);
 /* Stages the batch's pods on their devices without scanning. */
 int pm_batch_stage(pm_batch *);
 /* Scans the staged bytes again (no H2D); result as in pm_batch_wait. */

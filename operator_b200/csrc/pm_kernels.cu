@@ -1103,17 +1103,22 @@ __global__ void k_mark_unique(const unsigned long long *sorted, unsigned long lo
     if (i < n) flags[i] = (sorted[i] != ~0ull) && (i == 0 || sorted[i] != sorted[i - 1]);
 }
 
-// Ordering + de-duplication of the raw events when there are few of them (the normal case: hits
-// are ~1e-3 of lines; <= kSmallSort keys).  Three small launches that read their size from the
-// device counters, so the host need not learn the event count before it can enqueue the rest of
-// the pipeline:
-//   k_sort_chunks   16 CTAs, each bitonic-sorts one 1024-key chunk in shared memory
-//   k_sort_merge    every key finds its global rank by binary search in the other 15 chunks
+// Ordering + de-duplication of the raw events without host involvement (<= kMediumSort keys; hits
+// are ~1e-3 of lines, and 1e-2 of the lines of a 1 GiB batch still fit).  Every launch reads its size
+// from the device counters, so the host need not learn the event count before it can enqueue the
+// rest of the pipeline:
+//   k_sort_chunks   one CTA per 1024-key chunk that holds keys: bitonic sort in shared memory
+//   k_sort_merge    n <= kSmallSort: every key finds its global rank by binary search in the other
+//                   (at most 15) chunks, all of them in shared memory - one launch
+//   k_merge_all     n >  kSmallSort: seven rounds of pairwise run merges (1024 -> 131072 keys) in one launch, every
+//                   key finds its place in the merged run by one binary search in the sibling run
 //   k_sort_unique   one CTA drops duplicates and counts
-constexpr int kSortChunk = 1024, kSortChunks = kSmallSort / kSortChunk;
+// The launches of the path that does not apply return at once.
+constexpr int kSortChunk = 1024, kSortChunksSmall = kSmallSort / kSortChunk, kSortChunksMedium = kMediumSort / kSortChunk, kMergePasses = 7;
+static_assert((kSortChunk << kMergePasses) == kMediumSort, "merge passes must take 1024-key runs to kMediumSort");
 
 __device__ __forceinline__ bool sort_too_big(const ScanCounters *ctr, unsigned long long raw_cap) {
-    return ctr->cand_overflow || ctr->raw_overflow || ctr->n_raw > (unsigned long long)kSmallSort || ctr->n_raw > raw_cap;
+    return ctr->cand_overflow || ctr->raw_overflow || ctr->n_raw > (unsigned long long)kMediumSort || ctr->n_raw > raw_cap;
 }
 
 __global__ void __launch_bounds__(kSortChunk / 2) k_sort_chunks(const unsigned long long *__restrict__ raw, const ScanCounters *ctr, unsigned long long raw_cap,
@@ -1121,10 +1126,7 @@ __global__ void __launch_bounds__(kSortChunk / 2) k_sort_chunks(const unsigned l
     __shared__ unsigned long long keys[kSortChunk];
     if (sort_too_big(ctr, raw_cap)) return;
     const unsigned long long n = ctr->n_raw, base = (unsigned long long)blockIdx.x * kSortChunk;
-    if (base >= n) {   // empty chunk: all padding
-        for (unsigned i = threadIdx.x; i < kSortChunk; i += blockDim.x) chunks[base + i] = ~0ull;
-        return;
-    }
+    if (base >= n) return;   // no key in this chunk: the later stages stop at the last chunk that has one
     for (unsigned i = threadIdx.x; i < kSortChunk; i += blockDim.x) keys[i] = base + i < n ? raw[base + i] : ~0ull;
     __syncthreads();
     const unsigned t = threadIdx.x;
@@ -1147,6 +1149,7 @@ __global__ void __launch_bounds__(1024) k_sort_merge(const unsigned long long *_
     unsigned long long *sk = reinterpret_cast<unsigned long long *>(smem_raw);   // all sorted chunks (<= 128 KiB)
     if (sort_too_big(ctr, raw_cap)) return;
     const unsigned long long n = ctr->n_raw;
+    if (n > (unsigned long long)kSmallSort) return;   // k_merge_all takes it
     const unsigned n_chunks = (unsigned)((n + kSortChunk - 1) / kSortChunk);
     if (blockIdx.x * blockDim.x >= n_chunks * kSortChunk) return;
     for (unsigned k = threadIdx.x; k < n_chunks * kSortChunk / 2; k += blockDim.x) reinterpret_cast<uint4 *>(sk)[k] = reinterpret_cast<const uint4 *>(chunks)[k];
@@ -1171,6 +1174,63 @@ __global__ void __launch_bounds__(1024) k_sort_merge(const unsigned long long *_
     sorted[rank] = key;
 }
 
+// All seven rounds of pairwise run merges (1024 -> 131072 keys) in ONE launch, for 16384 < n <= 131072 keys; with
+// fewer keys the launch returns at once.  (As seven launches the rounds cost the common, small case 10 us: the sort
+// runs beside k_plan / k_check and is joined before k_finalize, and every launch on the busy GPU, even one with
+// nothing to do, adds its latency to that chain.)  A round: key i of run r goes to (start of the pair) + (its index in
+// r) + (number of keys of the sibling run that sort before it); ties go to the left run, so equal keys never collide.
+// The P = ceil(n / 1024) * 1024 keys that exist take part (the tail of the last chunk is +inf padding).  Rounds are
+// separated by a grid-wide barrier on a counter in the ScanCounters block (zeroed with it before every scan); the
+// grid is 128 CTAs of 256 threads, far below what the GPU keeps resident, and the kernels it shares the GPU with
+// finish on their own, so every CTA of this grid gets to run while the others wait.
+constexpr int kMergeCtas = 128, kMergeThreads = 256;
+
+__global__ void __launch_bounds__(kMergeThreads) k_merge_all(unsigned long long *__restrict__ buf_a, unsigned long long *__restrict__ buf_b, ScanCounters *ctr,
+                                                           unsigned long long raw_cap) {
+    if (sort_too_big(ctr, raw_cap)) return;
+    const unsigned long long n = ctr->n_raw;
+    if (n <= (unsigned long long)kSmallSort) return;   // k_sort_merge took it
+    const unsigned P = (unsigned)((n + kSortChunk - 1) / kSortChunk) * kSortChunk;
+    unsigned int *barrier = &ctr->merge_barrier;
+    for (int pass = 0; pass < kMergePasses; pass++) {
+        const unsigned long long *src = pass & 1 ? buf_b : buf_a;
+        unsigned long long *dst = pass & 1 ? buf_a : buf_b;
+        const unsigned run = (unsigned)kSortChunk << pass;
+        for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+            const unsigned long long key = __ldcg(src + i);   // written by other CTAs in the round before: read through L2
+            const unsigned r = i / run, sib = (r ^ 1u) * run;
+            if (sib >= P) {   // no sibling run: this run moves as it is
+                dst[i] = key;
+                continue;
+            }
+            const unsigned sib_end = min(sib + run, P);
+            unsigned lo = sib, hi = sib_end;
+            if (r & 1u) {   // right run: sibling keys <= key come first
+                while (lo < hi) {
+                    const unsigned mid = (lo + hi) >> 1;
+                    if (__ldcg(src + mid) <= key) lo = mid + 1; else hi = mid;
+                }
+            } else {        // left run: sibling keys < key come first
+                while (lo < hi) {
+                    const unsigned mid = (lo + hi) >> 1;
+                    if (__ldcg(src + mid) < key) lo = mid + 1; else hi = mid;
+                }
+            }
+            dst[(r & ~1u) * run + (i - r * run) + (lo - sib)] = key;
+        }
+        // grid-wide barrier
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(barrier, 1u);
+            const unsigned want = (unsigned)(pass + 1) * gridDim.x;
+            while (atomicAdd(barrier, 0u) < want) __nanosleep(64);
+            __threadfence();
+        }
+        __syncthreads();
+    }
+}
+
 __global__ void __launch_bounds__(1024) k_sort_unique(const unsigned long long *__restrict__ sorted, const ScanCounters *ctr, unsigned long long raw_cap,
                                                       unsigned long long *__restrict__ uniq, unsigned long long *n_unique, unsigned int *big_flag) {
     if (sort_too_big(ctr, raw_cap)) {
@@ -1181,25 +1241,25 @@ __global__ void __launch_bounds__(1024) k_sort_unique(const unsigned long long *
         return;
     }
     const unsigned n = (unsigned)ctr->n_raw;
-    constexpr unsigned per = kSmallSort / 1024;
-    // thread t owns the 16 consecutive keys [16t, 16t+16): one block scan of the per-thread counts
+    // thread t owns `per` consecutive keys: one block scan of the per-thread counts, then each thread writes its survivors
+    const unsigned per = (n + 1023u) / 1024u;
     const unsigned i0 = threadIdx.x * per;
-    unsigned long long k[per];
     unsigned long long prev = (i0 > 0 && i0 - 1 < n) ? sorted[i0 - 1] : ~0ull;
-    unsigned keep = 0, cnt = 0;
-#pragma unroll
-    for (unsigned r = 0; r < per; r++) {
-        k[r] = (i0 + r < n) ? sorted[i0 + r] : ~0ull;
-        bool kp = k[r] != ~0ull && (i0 + r == 0 || k[r] != prev);
-        prev = k[r];
-        keep |= (unsigned)kp << r;
-        cnt += kp;
+    const unsigned long long first_prev = prev;
+    unsigned cnt = 0;
+    for (unsigned r = 0; r < per && i0 + r < n; r++) {
+        const unsigned long long k = sorted[i0 + r];
+        cnt += (k != ~0ull && (i0 + r == 0 || k != prev));
+        prev = k;
     }
     __shared__ unsigned long long tot;
     unsigned long long at = block_exclusive_scan(cnt, &tot);
-#pragma unroll
-    for (unsigned r = 0; r < per; r++)
-        if (keep & (1u << r)) uniq[at++] = k[r];
+    prev = first_prev;
+    for (unsigned r = 0; r < per && i0 + r < n; r++) {
+        const unsigned long long k = sorted[i0 + r];
+        if (k != ~0ull && (i0 + r == 0 || k != prev)) uniq[at++] = k;
+        prev = k;
+    }
     if (threadIdx.x == 0) {
         *n_unique = tot;
         *big_flag = 0;
@@ -1213,15 +1273,15 @@ __global__ void __launch_bounds__(256) k_rank(const unsigned long long *__restri
                                               const unsigned long long *__restrict__ uniq, const unsigned long long *n_unique_ptr, uint32_t *__restrict__ rank) {
     if (sort_too_big(ctr, raw_cap)) return;
     const unsigned n = (unsigned)ctr->n_raw, nu = (unsigned)*n_unique_ptr;
-    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const unsigned long long key = raw[i];
-    unsigned lo = 0, hi = nu;   // lower bound; the key is present
-    while (lo < hi) {
-        const unsigned mid = (lo + hi) >> 1;
-        if (uniq[mid] < key) lo = mid + 1; else hi = mid;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned long long key = raw[i];
+        unsigned lo = 0, hi = nu;   // lower bound; the key is present
+        while (lo < hi) {
+            const unsigned mid = (lo + hi) >> 1;
+            if (uniq[mid] < key) lo = mid + 1; else hi = mid;
+        }
+        rank[i] = lo;
     }
-    rank[i] = lo;
 }
 
 // ------------------------------------------------------------------------------------ resolve (a12 + a13)
@@ -1866,15 +1926,16 @@ cudaError_t launch_export(EventOut src, EventOut dst_host, const unsigned long l
     return cudaGetLastError();
 }
 
-cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
+cudaError_t launch_sort_small(const unsigned long long *raw, ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
                               unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s) {
-    unsigned long long *chunks = scratch, *sorted = scratch + kSmallSort;
-    k_sort_chunks<<<kSortChunks, kSortChunk / 2, 0, s>>>(raw, ctr, raw_cap, chunks);
+    unsigned long long *buf_a = scratch, *buf_b = scratch + kMediumSort;
+    k_sort_chunks<<<kSortChunksMedium, kSortChunk / 2, 0, s>>>(raw, ctr, raw_cap, buf_a);
     cudaError_t e = cudaFuncSetAttribute(k_sort_merge, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSort * 8);
     if (e != cudaSuccess) return e;
-    k_sort_merge<<<kSmallSort / 1024, 1024, kSmallSort * 8, s>>>(chunks, ctr, raw_cap, sorted);
-    k_sort_unique<<<1, 1024, 0, s>>>(sorted, ctr, raw_cap, uniq, n_unique, big_flag);
-    k_rank<<<kSmallSort / 256, 256, 0, s>>>(raw, ctr, raw_cap, uniq, n_unique, reinterpret_cast<uint32_t *>(chunks));   // the chunk area is free again
+    k_sort_merge<<<kSortChunksSmall, 1024, kSmallSort * 8, s>>>(buf_a, ctr, raw_cap, buf_b);           // n <= kSmallSort, else returns at once
+    k_merge_all<<<kMergeCtas, kMergeThreads, 0, s>>>(buf_a, buf_b, ctr, raw_cap);                       // n >  kSmallSort, else returns at once
+    k_sort_unique<<<1, 1024, 0, s>>>(buf_b, ctr, raw_cap, uniq, n_unique, big_flag);                   // an odd number of passes: the result is in b
+    k_rank<<<64, 256, 0, s>>>(raw, ctr, raw_cap, uniq, n_unique, reinterpret_cast<uint32_t *>(buf_a));   // a is free again
     return cudaGetLastError();
 }
 

@@ -53,7 +53,8 @@ struct ScanCounters {                   // device-resident, zeroed before every 
     unsigned long long n_raw;           // raw events written by k_confirm / k_dfa_scan
     unsigned long long n_verified;      // literal confirmations that reached a verify DFA
     unsigned int cand_overflow, raw_overflow;
-    unsigned int pad[2];
+    unsigned int merge_barrier;         // grid-wide barrier of k_merge_all (arrivals, all rounds)
+    unsigned int pad;
 };
 
 struct PodDev {                         // per pod, device-resident
@@ -129,12 +130,13 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
                            const unsigned long long *uniq, const unsigned long long *n_unique_dev, unsigned long long ev_cap, EventOut out,
                            const ResolveScratch &rs, int num_sms, cudaStream_t s, cudaStream_t side = nullptr, cudaEvent_t fork_ev = nullptr,
                            cudaEvent_t join_ev = nullptr, cudaEvent_t uniq_ready = nullptr, const uint32_t *rank = nullptr);
-// Ordering + de-duplication without host involvement for ctr->n_raw <= kSmallSort (otherwise *big_flag = 1 and
-// the caller falls back to launch_sort_unique once it knows the count).
-constexpr int kSmallSort = 16384;
-// Four launches; `scratch` holds 2 * kSmallSort u64.  Afterwards the first kSmallSort u32 of `scratch` hold, for every raw key,
-// its rank in uniq (what k_finalize needs to place the key's row).
-cudaError_t launch_sort_small(const unsigned long long *raw, const ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
+// Ordering + de-duplication without host involvement for ctr->n_raw <= kMediumSort (otherwise *big_flag = 1 and
+// the caller falls back to launch_sort_unique once it knows the count).  Up to kSmallSort keys take one rank-merge
+// launch in shared memory, more take kMergePasses rounds of pairwise merges.
+constexpr int kSmallSort = 16384, kMediumSort = 131072;
+// Five launches (those of the path that does not apply return at once); `scratch` holds 2 * kMediumSort u64.  Afterwards the
+// first kMediumSort u32 of `scratch` hold, for every raw key, its rank in uniq (what k_finalize needs to place the key's row).
+cudaError_t launch_sort_small(const unsigned long long *raw, ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
                               unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s);
 // Gram profile: counts, for every aligned word of text[0, sample_bytes), the occurrences of the
 // keys of an open-addressing table (keys: 2^log2_cap u32, kGramEmpty = free; counts zeroed by the

@@ -241,6 +241,8 @@ struct PodRef {
     const uint8_t *ptr;
     size_t len, eff_len;
     uint64_t tag;
+    int on_device = -1;       // >= 0: `ptr` is device memory on that context device (pm_batch_add_pod_device); staged there, never cut
+    bool last_cr = false;     // the log ends in a lone '\r'
     int dev = 0, local = 0;   // device slot and index among that device's pods
     uint64_t start = 0;       // offset in the device text buffer
     // As a staged unit (pm_batch::units): which pod, which bytes of it, and how many lines of
@@ -425,6 +427,7 @@ int stage_impl(pm_batch *b) {
         const int first = (int)b->units.size();
         int pieces = split_force > 1 ? split_force : nd;
         if (split_min > 0) pieces = (int)std::min<size_t>((size_t)pieces, p.eff_len / split_min);
+        if (p.on_device >= 0) pieces = 1;   // the cut is made on host bytes
         if (pieces > 1) {
             const int halo = (b->lib->dev.empty() || b->lib->dev[0].ctx_slots <= 0) ? 64 : b->lib->dev[0].ctx_slots;
             std::vector<SplitUnit> cut;   // pm_split.cc
@@ -434,6 +437,7 @@ int stage_impl(pm_batch *b) {
                 u.ptr = p.ptr + c.begin;
                 u.len = c.end - c.begin;
                 u.eff_len = effective_len(u.ptr, u.len);
+                u.last_cr = u.len && u.ptr[u.len - 1] == '\r';
                 u.pod = (int)i;
                 u.begin = c.begin;
                 u.lead = c.lead;
@@ -452,7 +456,13 @@ int stage_impl(pm_batch *b) {
     for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
     std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return b->units[x].len > b->units[y].len; });
     std::vector<uint64_t> load(nd, 0);
+    for (const PodRef &u : b->units)
+        if (u.on_device >= 0) load[u.on_device] += u.len + 64;   // device-resident pods stay where they are
     for (int i : order) {
+        if (b->units[i].on_device >= 0) {
+            b->units[i].dev = b->units[i].on_device;
+            continue;
+        }
         int best = 0;
         for (int d = 1; d < nd; d++)
             if (load[d] < load[best]) best = d;
@@ -553,7 +563,7 @@ int stage_impl(pm_batch *b) {
             hp[k].nl_before = 0;
             hp[k].n_lines = 0;
             hp[k].pad = 0;
-            if (p.len && p.ptr[p.len - 1] == '\r') w.any_trailing_cr = 1;
+            if (p.last_cr) w.any_trailing_cr = 1;
             off = round_up(off + p.len + 1, 16);   // >= 1 byte of '\n' padding
         }
         // content end, rounded to a tile, plus one full tile of '\n' so that 512-byte look-ahead
@@ -578,7 +588,7 @@ int stage_impl(pm_batch *b) {
         CU(cudaEventRecord(w.e[0], w.stream));
         for (int k = 0; k < np; k++) {
             PodRef &p = b->units[w.pods[k]];
-            if (p.len) CU(cudaMemcpyAsync(w.text.as<uint8_t>() + p.start, p.ptr, p.len, cudaMemcpyHostToDevice, w.stream));
+            if (p.len) CU(cudaMemcpyAsync(w.text.as<uint8_t>() + p.start, p.ptr, p.len, p.on_device >= 0 ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, w.stream));
         }
         CU(cudaEventRecord(w.e[1], w.stream));
         CU(launch_pad(w.text.as<uint8_t>(), w.pods_dev.as<PodDev>(), np, w.total, w.stream));
@@ -717,10 +727,10 @@ int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
     if ((rc = get(d->pool, w.item_cap * resolve_item_bytes(), w.rs_items))) return rc;
     if ((rc = get(d->pool, w.item_cap, w.rs_results))) return rc;
     if ((rc = get(d->pool, w.long_cap * 4, w.rs_long))) return rc;
-    // the resolve stage plans either the sorted events (<= ev_cap) or the raw queue (<= kSmallSort)
-    w.key_cap = std::max<uint64_t>(ev_cap, std::min<uint64_t>(w.raw_cap, kSmallSort));
+    // the resolve stage plans either the sorted events (<= ev_cap) or the raw queue (<= kMediumSort)
+    w.key_cap = std::max<uint64_t>(ev_cap, std::min<uint64_t>(w.raw_cap, kMediumSort));
     if ((rc = get(d->pool, w.key_cap * resolve_aux_bytes(), w.rs_aux))) return rc;
-    if ((rc = get(d->pool, ev_cap * 8 + 64, w.uniq))) return rc;
+    if ((rc = get(d->pool, w.key_cap * 8 + 64, w.uniq))) return rc;   // the on-device sort may deliver up to key_cap unique keys, whatever ev_cap is
     return PM_OK;
 }
 
@@ -735,7 +745,7 @@ int enqueue_resolve(pm_batch *b, DevWork &w, bool from_raw = false) {
     const unsigned long long *n_unique = reinterpret_cast<const unsigned long long *>(w.ctr.as<char>() + kOffUnique);
     const unsigned long long *keys = from_raw ? w.raw.as<unsigned long long>() : w.uniq.as<unsigned long long>();
     const unsigned long long *n_keys = from_raw ? &w.ctr.as<ScanCounters>()->n_raw : n_unique;
-    const uint64_t key_cap = from_raw ? std::min<uint64_t>(w.raw_cap, kSmallSort) : w.ev_cap;
+    const uint64_t key_cap = from_raw ? std::min<uint64_t>(w.raw_cap, kMediumSort) : w.ev_cap;
     CU(launch_resolve(w.text.as<uint8_t>(), dl, w.tile_prefix.as<unsigned long long>(), w.table(), keys, n_keys, key_cap,
                       w.uniq.as<unsigned long long>(), n_unique, w.ev_cap, L.on(w.ev_soa.p), rs, w.sms_post, w.stream, w.stream2, w.fork_ev[1],
                       w.join_ev[1], from_raw ? w.join_ev[2] : nullptr, from_raw ? w.sort_scratch.as<uint32_t>() : nullptr));
@@ -748,7 +758,7 @@ int enqueue_resolve(pm_batch *b, DevWork &w, bool from_raw = false) {
     // engines do it instead: they cost no SM, and an SM is what the other batches are waiting for
     // (measured: 1 % more throughput than with the kernel).  PM_RESULT_MEMCPY=1 forces the copy engines.
     static const bool force_copy_engine = getenv("PM_RESULT_MEMCPY") != nullptr;
-    const bool copy_engine = force_copy_engine || b->ctx->devs[w.slot]->depth > 1;
+    const bool copy_engine = force_copy_engine || (b->ctx->devs[w.slot]->depth > 1 && w.ev_cap <= kSmallSort);   // a large capacity is mostly empty: copy what there is
     if (copy_engine) {
         CU(cudaMemcpyAsync(w.h_soa.p, w.ev_soa.p, L.bytes, cudaMemcpyDeviceToHost, w.stream));
         CU(cudaMemcpyAsync(w.h_ctr.p, w.ctr.p, kCtrBytes, cudaMemcpyDeviceToHost, w.stream));
@@ -778,8 +788,10 @@ int scan_async(pm_batch *b) {
         const int np = (int)w.pods.size();
         // capacity of the result arrays: everything the small sort can deliver on the first scan of a
         // batch, the last event count plus 12 % on a re-scan (less to copy back)
-        uint64_t want = kSmallSort;
-        if (w.scanned) want = std::min<uint64_t>(kSmallSort, round_up(w.n_events + w.n_events / 8 + 64, 256));
+        // (first scan: what the on-device sort can deliver for a batch of this size at a hit rate of 1e-2 of its lines;
+        // a batch with more events than that comes back once with the count and repeats the resolve stage)
+        uint64_t want = std::min<uint64_t>(kMediumSort, std::max<uint64_t>(kSmallSort, round_up(w.total / 8192, 1024)));
+        if (w.scanned) want = std::min<uint64_t>(kMediumSort, round_up(w.n_events + w.n_events / 8 + 64, 256));
         int rc = ensure_resolve_scratch(b, w, want);
         if (rc) return rc;
         CU(cudaMemsetAsync(w.ctr.p, 0, kCtrBytes, w.stream));
@@ -790,7 +802,7 @@ int scan_async(pm_batch *b) {
             CU(cudaStreamWaitEvent(ss, w.scan_fork, 0));
         }
         if ((rc = get(d->pool, w.raw_cap * 8, w.tasks))) return rc;
-        if ((rc = get(d->pool, 2 * (size_t)kSmallSort * 8, w.sort_scratch))) return rc;
+        if ((rc = get(d->pool, 2 * (size_t)kMediumSort * 8, w.sort_scratch))) return rc;
         CU(cudaEventRecord(w.e[2], ss));
         CU(launch_scan(w.text.as<uint8_t>(), w.n_tiles, dl, w.tile_nl.as<uint32_t>(), w.cand.as<unsigned long long>(), w.cand_cap,
                        w.ctr.as<ScanCounters>(), w.sms_scan, ss));
@@ -831,7 +843,7 @@ int scan_async(pm_batch *b) {
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
                              reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream3));
         CU(cudaEventRecord(w.join_ev[2], w.stream3));
-        w.launches += 4;
+        w.launches += 5;
         CU(cudaStreamWaitEvent(w.stream, w.join_ev[0], 0));
         w.mark("join prefix/pods");
         CU(cudaEventRecord(w.e[4], w.stream));
@@ -1350,7 +1362,57 @@ int pm_batch_add_pod(pm_batch *b, const uint8_t *log, size_t n, uint64_t tag) {
     p.ptr = log;
     p.len = n;
     p.eff_len = effective_len(log, n);
+    p.last_cr = n && log[n - 1] == '\r';
     p.tag = tag;
+    b->pods.push_back(p);
+    return PM_OK;
+}
+
+int pm_batch_add_pod_device(pm_batch *b, const void *d_log, size_t n, uint64_t tag) {
+    if (!b || (!d_log && n)) return fail(PM_E_INVALID, "null argument");
+    if (b->staged) return fail(PM_E_INVALID, "batch already staged");
+    PodRef p;
+    p.ptr = static_cast<const uint8_t *>(d_log);
+    p.len = n;
+    p.tag = tag;
+    // which of the context's devices holds the bytes
+    int ordinal = -1;
+    if (n) {
+        cudaPointerAttributes at;
+        CU(cudaPointerGetAttributes(&at, d_log));
+        if (at.type != cudaMemoryTypeDevice) return fail(PM_E_INVALID, "pm_batch_add_pod_device: not a device pointer (use pm_batch_add_pod for host memory)");
+        ordinal = at.device;
+    } else {
+        CU(cudaGetDevice(&ordinal));
+    }
+    for (size_t k = 0; k < b->ctx->devs.size(); k++)
+        if (b->ctx->devs[k]->id == ordinal) p.on_device = (int)k;
+    if (p.on_device < 0) {
+        if (n) return fail(PM_E_INVALID, "pm_batch_add_pod_device: the pointer lives on device %d, which this context does not own", ordinal);
+        p.on_device = 0;
+    }
+    // Java's split drops trailing "\r?\n" separators: look at the end of the log, 4 KiB at a time.  A byte is kept
+    // when it is neither '\r' nor '\n', or a '\r' that is not followed by '\n'; the effective end is behind the last kept byte.
+    CU(cudaSetDevice(ordinal));
+    std::vector<uint8_t> tail(4097);
+    size_t eff = 0, hi = n;
+    bool found = false;
+    while (hi > 0 && !found) {
+        const size_t lo = hi > 4096 ? hi - 4096 : 0, upto = std::min(n, hi + 1);
+        CU(cudaMemcpy(tail.data(), p.ptr + lo, upto - lo, cudaMemcpyDeviceToHost));
+        for (size_t i = hi; i-- > lo;) {
+            const uint8_t c = tail[i - lo];
+            const bool keep = (c != '\r' && c != '\n') || (c == '\r' && (i + 1 == n || tail[i + 1 - lo] != '\n'));
+            if (keep) {
+                eff = i + 1;
+                found = true;
+                break;
+            }
+        }
+        if (hi == n) p.last_cr = tail[n - 1 - lo] == '\r';
+        hi = lo;
+    }
+    p.eff_len = eff;
     b->pods.push_back(p);
     return PM_OK;
 }

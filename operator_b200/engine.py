@@ -70,7 +70,7 @@ ABI_SYMBOLS = ["pm_abi_version", "pm_init", "pm_init_devices", "pm_shutdown", "p
                "pm_library_publish", "pm_library_free", "pm_library_pattern_count", "pm_library_pattern_meta_json",
                "pm_host_alloc", "pm_host_free", "pm_batch_begin", "pm_batch_add_pod", "pm_batch_submit", "pm_batch_wait",
                "pm_batch_release", "pm_batch_stage", "pm_batch_rescan", "pm_batch_line_index", "pm_parse",
-               "pm_line_index_noalloc", "pm_noalloc_last_error", "pm_set_pipeline", "pm_parse_stats", "pm_library_serialize", "pm_library_load"]
+               "pm_line_index_noalloc", "pm_noalloc_last_error", "pm_batch_add_pod_device", "pm_set_pipeline", "pm_parse_stats", "pm_library_serialize", "pm_library_load"]
 
 
 def load_library() -> ctypes.CDLL:
@@ -105,6 +105,7 @@ def load_library() -> ctypes.CDLL:
     d.pm_host_free.restype = None
     d.pm_batch_begin.argtypes = [vp, _P(vp)]
     d.pm_batch_add_pod.argtypes = [vp, vp, sz, ctypes.c_uint64]
+    d.pm_batch_add_pod_device.argtypes = [vp, vp, sz, ctypes.c_uint64]
     d.pm_batch_submit.argtypes = [vp]
     d.pm_batch_wait.argtypes = [vp, _P(ResultView)]
     d.pm_batch_release.argtypes = [vp]
@@ -229,6 +230,12 @@ class Batch:
             self._keep.append(buf)
             ptr, n = ctypes.addressof(buf), len(log)
         _check(load_library().pm_batch_add_pod(self._h, ptr, n, tag))
+
+    def add_pod_device(self, device_ptr: int, nbytes: int, tag: int = 0, keep: object = None):
+        """A pod that already lives in device memory (pm_batch_add_pod_device); `keep` is whatever owns it."""
+        if keep is not None:
+            self._keep.append(keep)
+        _check(load_library().pm_batch_add_pod_device(self._h, device_ptr, nbytes, tag))
 
     def submit(self):
         _check(load_library().pm_batch_submit(self._h))

@@ -172,6 +172,37 @@ def make_library(n_patterns: int, seed: int = LIB_SEED, library_id: str = "synth
     return lib, wit, swit
 
 
+# Short-literal and class-led primaries: what a hand-written library adds to the long phrases above
+# ("\\bOOM\\b", "exit code \\d+", "(?i)error \\d+", "[Cc]ache (evicted|flushed)").  (regex, witness)
+SHORT_CODES = ["OOM", "NPE", "EOF", "ANR", "SIGV", "ENOSPC", "EPIPE", "ECONNR", "EAGAIN", "E5XX", "OOMK", "DLQ", "GCX", "SSLX", "TLSX"]
+SHORT_PRIMARIES = (
+    [("\\b%s\\b" % c, "worker hit %s again" % c) for c in SHORT_CODES] +
+    [("exit code %d\\b" % n, "process finished with exit code %d" % n) for n in (1, 2, 3, 126, 127, 134, 137, 139, 143, 255)] +
+    [("(?i)%s \\d+" % w, "%s %d" % (w.upper(), 17 + i)) for i, w in enumerate(("errno", "fault", "abort", "crash", "fatal"))] +
+    [("[%s%s]%s (evicted|flushed)" % (w[0].upper(), w[0], w[1:]), "%s evicted" % w) for w in ("cache", "buffer", "queue", "journal", "ledger")] +
+    [("\\b%s\\d{3,4}\\b" % p_, "code %s%d seen" % (p_, 4000 + i)) for i, p_ in enumerate(("ERR-", "QK", "HHH", "RESTEASY", "SRMSG"))] +
+    [("killed by signal %d" % n, "child killed by signal %d" % n) for n in (6, 9, 11, 15)] +
+    [("%s: " % w, "goroutine 1 %s: nil map" % w) for w in ("panic", "fatal", "abort")] +
+    [("status=5\\d\\d", "upstream status=503 retry"), ("\\btimed? ?out\\b", "request timed out"), ("(?i)segfault", "SEGFAULT at 0x0")]
+)
+
+
+def make_mixed_library(n_patterns: int, fraction: float = 0.1, seed: int = LIB_SEED) -> Tuple[dict, List[str], List[Optional[str]]]:
+    """make_library with every (1/fraction)-th primary replaced by a short-literal / class-led regex."""
+    lib, wit, swit = make_library(n_patterns, seed, "synthetic-mixed")
+    step = max(1, int(round(1.0 / fraction)))
+    k = 0
+    for i in range(0, n_patterns, step):
+        rx, w = SHORT_PRIMARIES[k % len(SHORT_PRIMARIES)]
+        if k >= len(SHORT_PRIMARIES):      # more slots than templates: make the regex distinct
+            rx, w = rx + " r%d" % k, w + " r%d" % k
+        lib["patterns"][i]["primary_pattern"]["regex"] = rx
+        lib["patterns"][i]["name"] = "short: " + rx
+        wit[i] = w
+        k += 1
+    return lib, wit, swit
+
+
 # --------------------------------------------------------------------------- native corpus generator
 _lib = None
 
@@ -191,12 +222,25 @@ def _native():
     return _lib
 
 
+def near_misses(witnesses: List[str]) -> List[str]:
+    """Strings that share vocabulary and literals with the witnesses without (in general) matching their
+    patterns: every witness with its tail cut off, and with its head cut off."""
+    out = []
+    for w in witnesses:
+        out.append(w[:max(8, int(len(w) * 0.7))])
+        out.append(w[int(len(w) * 0.35):])
+    return out
+
+
 def make_corpus(target_bytes: int, witnesses: List[str], sec_witnesses: Optional[List[Optional[str]]] = None,
                 p_hit: float = 1e-3, seed: int = LOG_SEED, first_line: int = 0, crlf: bool = False,
-                out: Optional[np.ndarray] = None, threads: int = 0) -> Tuple[np.ndarray, int]:
+                out: Optional[np.ndarray] = None, threads: int = 0, p_near: float = 0.0,
+                near: Optional[List[str]] = None) -> Tuple[np.ndarray, int]:
     """Generates <= target_bytes of Quarkus/JVM-style log text ending in a newline.
-    Returns (uint8 array view of the bytes written, number of lines)."""
+    Returns (uint8 array view of the bytes written, number of lines).  p_near / near: near-miss lines."""
     lib = _native()
+    if p_near > 0 and near:
+        return _make_corpus_near(lib, target_bytes, witnesses, sec_witnesses, p_hit, seed, first_line, crlf, out, threads, p_near, near)
     n = len(witnesses)
     W = (ctypes.c_char_p * max(n, 1))(*[w.encode() for w in witnesses])
     sw = sec_witnesses or [None] * n
@@ -210,3 +254,53 @@ def make_corpus(target_bytes: int, witnesses: List[str], sec_witnesses: Optional
     if got < 0:
         raise RuntimeError("pm_synth_corpus failed")
     return out[:got], nl.value
+
+
+def _make_corpus_near(lib, target_bytes, witnesses, sec_witnesses, p_hit, seed, first_line, crlf, out, threads, p_near, near):
+    if not hasattr(lib, "_near_ready"):
+        lib.pm_synth_corpus_near.restype = ctypes.c_int64
+        lib.pm_synth_corpus_near.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int64, ctypes.c_double,
+                                             ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_char_p), ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_double, ctypes.POINTER(ctypes.c_char_p), ctypes.c_int,
+                                             ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
+        lib._near_ready = True
+    n = len(witnesses)
+    W = (ctypes.c_char_p * max(n, 1))(*[w.encode() for w in witnesses])
+    sw = sec_witnesses or [None] * n
+    S = (ctypes.c_char_p * max(n, 1))(*[(x.encode() if x else None) for x in sw])
+    N = (ctypes.c_char_p * len(near))(*[x.encode() for x in near])
+    if out is None:
+        out = np.empty(target_bytes, dtype=np.uint8)
+    nl = ctypes.c_int64(0)
+    got = lib.pm_synth_corpus_near(seed, first_line, target_bytes, p_hit, W, S, n, int(crlf), p_near, N, len(near),
+                                   out.ctypes.data, ctypes.byref(nl), threads)
+    if got < 0:
+        raise RuntimeError("pm_synth_corpus_near failed")
+    return out[:got], nl.value
+
+
+def make_corpus_device(device_ptr: int, target_bytes: int, witnesses: List[str], sec_witnesses: Optional[List[Optional[str]]] = None,
+                       p_hit: float = 1e-3, seed: int = LOG_SEED, first_line: int = 0, crlf: bool = False, p_near: float = 0.0,
+                       near: Optional[List[str]] = None) -> Tuple[int, int]:
+    """The same corpus as make_corpus, written by the GPU into device memory at `device_ptr` (at least
+    target_bytes bytes on the current CUDA device).  Returns (bytes written, number of lines)."""
+    lib = _native()
+    if not hasattr(lib, "_dev_ready"):
+        lib.pm_synth_corpus_device_near.restype = ctypes.c_int64
+        lib.pm_synth_corpus_device_near.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int64, ctypes.c_double,
+                                                    ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_char_p), ctypes.c_int, ctypes.c_int,
+                                                    ctypes.c_double, ctypes.POINTER(ctypes.c_char_p), ctypes.c_int,
+                                                    ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]
+        lib._dev_ready = True
+    n = len(witnesses)
+    w = (ctypes.c_char_p * max(n, 1))(*[x.encode("utf-8") for x in witnesses])
+    sec = sec_witnesses or [None] * n
+    sw = (ctypes.c_char_p * max(n, 1))(*[(x.encode("utf-8") if x else None) for x in sec])
+    n_lines = ctypes.c_int64(0)
+    near = near or []
+    nm = (ctypes.c_char_p * max(len(near), 1))(*[x.encode("utf-8") for x in near])
+    got = lib.pm_synth_corpus_device_near(seed, first_line, target_bytes, p_hit, w, sw, n, 1 if crlf else 0, p_near if near else 0.0, nm, len(near),
+                                          device_ptr, ctypes.byref(n_lines))
+    if got < 0:
+        raise RuntimeError("pm_synth_corpus_device failed (%d)" % got)
+    return int(got), int(n_lines.value)

@@ -95,21 +95,59 @@ typedef struct {
     int64_t cap, n;
 } job;
 
+typedef struct {
+    int64_t line;
+    int32_t pat;
+} hit;
+
+static int hit_cmp(const void *a, const void *b) {
+    const hit *x = a, *y = b;
+    if (x->line != y->line) return x->line < y->line ? -1 : 1;
+    return x->pat < y->pat ? -1 : x->pat > y->pat;
+}
+
+static void emit(job *j, int64_t line, int32_t pat) {
+    if (j->n < j->cap) {
+        j->out_line[j->n] = line;
+        j->out_pat[j->n] = pat;
+    }
+    j->n++;
+}
+
 static void *worker(void *arg) {
     job *j = arg;
     pcre2_match_data **md = calloc((size_t)j->lib->n, sizeof *md);
     for (int p = 0; p < j->lib->n; p++) md[p] = p_md_create(j->lib->code[p], NULL);
-    for (int64_t i = j->a; i < j->b; i++)
-        for (int p = 0; p < j->lib->n; p++) {
-            int rc = p_match(j->lib->code[p], j->log + j->starts[i], (size_t)j->lens[i], 0, PCRE2_NO_UTF_CHECK, md[p], NULL);
-            if (rc >= 0) {
-                if (j->n < j->cap) {
-                    j->out_line[j->n] = i;
-                    j->out_pat[j->n] = p;
-                }
-                j->n++;
+    if (j->lib->n <= 2000) {
+        /* the reference's shape: for every line, every pattern */
+        for (int64_t i = j->a; i < j->b; i++)
+            for (int p = 0; p < j->lib->n; p++) {
+                int rc = p_match(j->lib->code[p], j->log + j->starts[i], (size_t)j->lens[i], 0, PCRE2_NO_UTF_CHECK, md[p], NULL);
+                if (rc >= 0) emit(j, i, p);
             }
+    } else {
+        /* Large libraries (config 4: 20 000 patterns, ~20 MB of JIT code): the same (line, pattern) searches in blocks of
+         * 1024 lines with the pattern loop outside, so that a pattern's code is fetched once per block instead of once
+         * per line.  The hits of a block are put back in (line, pattern) order before they are emitted. */
+        enum { BLOCK = 1024 };
+        size_t hcap = 4096, hn;
+        hit *hits = malloc(hcap * sizeof *hits);
+        for (int64_t b0 = j->a; b0 < j->b; b0 += BLOCK) {
+            const int64_t b1 = b0 + BLOCK < j->b ? b0 + BLOCK : j->b;
+            hn = 0;
+            for (int p = 0; p < j->lib->n; p++)
+                for (int64_t i = b0; i < b1; i++) {
+                    int rc = p_match(j->lib->code[p], j->log + j->starts[i], (size_t)j->lens[i], 0, PCRE2_NO_UTF_CHECK, md[p], NULL);
+                    if (rc >= 0) {
+                        if (hn == hcap) hits = realloc(hits, (hcap *= 2) * sizeof *hits);
+                        hits[hn].line = i, hits[hn].pat = p, hn++;
+                    }
+                }
+            qsort(hits, hn, sizeof *hits, hit_cmp);
+            for (size_t k = 0; k < hn; k++) emit(j, hits[k].line, hits[k].pat);
         }
+        free(hits);
+    }
     for (int p = 0; p < j->lib->n; p++) p_md_free(md[p]);
     free(md);
     return NULL;

@@ -5,7 +5,7 @@ logs and pipeline depths, every result compared with the oracle.  Run on a GPU b
 
 Round 1: 757 synthetic configurations / 62 705 events in 200 s and 107 hand-written-regex configurations /
 20 291 events in 150 s (both tiers, secondaries, long lines, CRLF), all bit-exact."""
-import sys, random, time
+import sys, random, signal, time
 import os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from operator_b200 import Engine, synth
@@ -79,7 +79,60 @@ def soak_handwritten(seed, seconds):
     print("soak (hand-written) ok: %d configurations, %d events" % (n, ev))
 
 
+def soak_fuzz(seed, seconds):
+    """Third mode (`python tests/soak_parity.py <seed> <seconds> fuzz`): libraries drawn from the grammar-based generator
+    of tests/regex_fuzz.py (what the CPU three-way test runs through Python re, PCRE2 and the host DFA walk), as
+    primaries and secondaries, over logs made of their own samples, near misses and noise - through the kernels."""
+    from tests import regex_fuzz
+    from tests.test_gpu_parity import check_parity, lib_of
+    rnd = random.Random(seed)
+    eng = Engine(1)
+    t0 = time.time(); n = 0; ev = 0; skipped = 0; slow = 0
+
+    class OracleTooSlow(Exception):
+        pass
+
+    def on_alarm(signum, frame):
+        raise OracleTooSlow()
+
+    signal.signal(signal.SIGALRM, on_alarm)
+    while time.time() - t0 < seconds:
+        nodes = [regex_fuzz.random_regex(rnd) for _ in range(rnd.randint(1, 10))]
+        regs = [nd.regex() for nd in nodes]
+        lib = lib_of(regs, context_extraction={"lines_before": rnd.randint(0, 4), "lines_after": rnd.randint(0, 6), "include_stack_trace": rnd.random() < 0.3})
+        for p in lib["patterns"]:
+            if rnd.random() < 0.3:
+                p["secondary_patterns"] = [{"regex": regex_fuzz.random_regex(rnd).regex(), "weight": 0.25, "proximity_window": rnd.randint(1, 8)}]
+        logs = []
+        for _ in range(rnd.choice([1, 3])):
+            lines = []
+            for nd in nodes:
+                lines += regex_fuzz.lines_for(nd, rnd, rnd.choice([4, 16]))
+            rnd.shuffle(lines)
+            sep = "\r\n" if rnd.random() < 0.3 else "\n"
+            logs.append((sep.join(lines) + sep).encode("utf-8"))
+        eng.set_pipeline(rnd.choice([1, 1, 3]), 0)
+        # The oracle is a backtracking engine (Python re): a drawn regex with nested alternations can take it minutes on a
+        # near miss.  The kernels do not care, but there is nothing to compare with then: give the oracle 20 s per configuration.
+        signal.alarm(20)
+        try:
+            res = check_parity(eng, lib, logs)
+        except OracleTooSlow:
+            slow += 1
+            continue
+        except Exception as e:
+            if any(k in str(e) for k in ("nullable", "UNSUPPORTED", "SYNTAX", "TOO_COMPLEX", "never match")):
+                skipped += 1
+                continue          # a drawn regex outside the subset (e.g. one that can match the empty string): rejected, as documented
+            raise
+        finally:
+            signal.alarm(0)
+        n += 1; ev += res.n_events
+    print("soak (fuzz) ok: %d configurations, %d events, %d libraries rejected by the compiler, %d dropped because the oracle was too slow" % (n, ev, skipped, slow))
+
+
 if __name__ == "__main__":
     seed = int(sys.argv[1]) if len(sys.argv) > 1 else 1
     seconds = float(sys.argv[2]) if len(sys.argv) > 2 else 120
-    (soak_handwritten if len(sys.argv) > 3 and sys.argv[3] == "hand" else soak_synthetic)(seed, seconds)
+    mode = sys.argv[3] if len(sys.argv) > 3 else "synthetic"
+    {"hand": soak_handwritten, "fuzz": soak_fuzz}.get(mode, soak_synthetic)(seed, seconds)

@@ -74,6 +74,18 @@ def test_large_library_20k_patterns(engine):
     got_head = [t for t in _got(res, 0) if t[2] < len(head)]
     assert [t[:2] for t in got_head] == [(e.line_no, e.pattern) for e in ev]
     assert [t[8] for t in got_head] == [e.score for e in ev]
+    # 64 MiB at the benchmark's hit density: every (line, pattern) pair against the PCRE2 loop (~9.4e9 regex searches
+    # on the host cores, about half a minute)
+    corpus, n_lines = synth.make_corpus(64 << 20, wit, swit, p_hit=1e-3, first_line=1 << 40)
+    res = engine.scan([corpus])
+    starts, lens = pcre2_oracle.split(corpus)
+    ol, op, total = pcre2_oracle.scan(pl, corpus, starts, lens, threads=os.cpu_count() or 4)
+    assert total == ol.size
+    want = np.stack([ol + 1, op.astype(np.int64)], axis=1)
+    want = want[np.lexsort((want[:, 1], want[:, 0]))]
+    got = np.stack([res.line_no.astype(np.int64), res.pattern_index.astype(np.int64)], axis=1)
+    assert want.shape[0] > 300 and np.array_equal(got, want)
+    pl.close()
 
 
 def test_crash_storm_many_small_pods(engine):
@@ -204,3 +216,36 @@ def test_one_large_log_is_cut_across_devices(tmp_path):
     env = dict(os.environ, PM_SPLIT_FORCE="3", PM_SPLIT_MIN_BYTES="60000")
     r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0 and "split ok" in r.stdout, r.stdout[-1500:] + r.stderr[-2500:]
+
+
+def test_device_generator_is_byte_identical_and_device_pods_scan_alike(engine):
+    """The corpus generator as a kernel (configs 3 and 5 generate their text where it is scanned) writes
+    exactly the host generator's bytes, and a pod handed over as a device pointer gives the events of
+    the same pod handed over as host bytes."""
+    import torch
+    lib_json, wit, swit = synth.make_library(50)
+    engine.compile_library(lib_json).publish()
+    for target, kw in ((64 << 20, dict(p_hit=1e-3)), (5 << 20, dict(p_hit=0.02, crlf=True, first_line=(3 << 36) + 17)), (1000, dict(p_hit=0.5)), (5, dict())):
+        host, host_lines = synth.make_corpus(target, wit, swit, **kw)
+        dev = torch.empty(max(target, 1), dtype=torch.uint8, device="cuda")
+        got, dev_lines = synth.make_corpus_device(dev.data_ptr(), target, wit, swit, **kw)
+        assert (got, dev_lines) == (int(host.size), host_lines)
+        assert np.array_equal(dev[:got].cpu().numpy(), host)
+    host, _ = synth.make_corpus(6 << 20, wit, swit, p_hit=2e-3)
+    raw = bytes(host).rstrip(b"\n") + b"\r\n\n\r\n"      # trailing separators are dropped on the device side too
+    want = engine.scan([raw, b"", raw[:100000] + b"\r"])
+    d0 = torch.frombuffer(bytearray(raw), dtype=torch.uint8).cuda()
+    d2 = torch.frombuffer(bytearray(raw[:100000] + b"\r"), dtype=torch.uint8).cuda()
+    b = engine.batch()
+    try:
+        b.add_pod_device(d0.data_ptr(), d0.numel(), 0, keep=d0)
+        b.add_pod_device(0, 0, 1)
+        b.add_pod_device(d2.data_ptr(), d2.numel(), 2, keep=d2)
+        b.submit()
+        got = b.wait()
+    finally:
+        b.release()
+    assert got.n_events == want.n_events and want.n_events > 0
+    assert got.pod_n_lines.tolist() == want.pod_n_lines.tolist()
+    for name in ("pod_index", "pattern_index", "line_no", "line_start", "line_len", "ctx_first_line", "ctx_last_line", "ctx_start", "ctx_end", "score"):
+        assert np.array_equal(getattr(got, name), getattr(want, name)), name

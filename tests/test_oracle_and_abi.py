@@ -131,7 +131,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(dll, s), s
     assert sorted(engine.ABI_SYMBOLS) == [s for s in syms if s in engine.ABI_SYMBOLS]
     assert set(engine.ABI_SYMBOLS) <= set(syms)
-    assert dll.pm_abi_version() == 2
+    assert dll.pm_abi_version() == 3
 
 
 def test_signatures_carry_no_torch_types():

@@ -22,7 +22,10 @@ def main():
     ap.add_argument("--patterns", type=int, default=500)
     ap.add_argument("--p-hit", type=float, default=1e-3)
     ap.add_argument("--tag", default="")
+    ap.add_argument("--stages", action="store_true", help="also print the per-stage device times of one more step (PM_DEBUG_TIMING marks)")
     args = ap.parse_args()
+    if args.stages:
+        os.environ["PM_DEBUG_TIMING"] = "1"   # read once, when the library records its first mark
     torch.cuda.set_device(0)
     eng = Engine(devices=[0])
     lib_json, wit, swit = synth.make_library(args.patterns)
@@ -53,6 +56,23 @@ def main():
     print(json.dumps({"tag": args.tag, "env": {k_: v for k_, v in os.environ.items() if k_.startswith("PM_")}, "ms_step": tot / k, "ms_scan": scan / k,
                       "ms_post": post / k, "gbs": nbytes / (tot / k) / 1e6, "wall_ms_per_step": e0.elapsed_time(e1) / k, "events": int(r.n_events),
                       "cand": int(r.n_candidates), "verified": int(r.n_verified), "launches": int(r.gpu_launches), "fingerprint": fp}), flush=True)
+    if args.stages:
+        # the marks of a step are printed to stderr when it finishes: catch them for one step
+        import re
+        import sys
+        import tempfile
+        with tempfile.TemporaryFile(mode="w+") as tmp:
+            sys.stderr.flush()
+            saved = os.dup(2)
+            os.dup2(tmp.fileno(), 2)
+            try:
+                b.rescan(copy=False)
+            finally:
+                os.dup2(saved, 2)
+                os.close(saved)
+            tmp.seek(0)
+            stages = [(m.group(1).strip(), float(m.group(2))) for m in re.finditer(r"\[pm timing\] (.+?)\s+([0-9.]+) us", tmp.read())]
+        print(json.dumps({"tag": args.tag, "stages_us": stages, "note": "every mark is an event record on the main stream and adds ~2 us"}), flush=True)
     b.release()
     pinned.free()
     eng.close()
