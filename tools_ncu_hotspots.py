@@ -4,7 +4,7 @@
 for the cubin of the same build.
 
     cuobjdump -xelf all operator_b200/csrc/pm_kernels.o          # -> pm_kernels.sm_100a.cubin (run in /tmp/cub)
-    python tools_ncu_hotspots.py k_planE gpurun_out/post_r02.ncu-rep 30
+    python tools_ncu_hotspots.py k_planE gpurun_out/post_r02.ncu-rep 30 [ncu kernel-name regex, default: the mangled fragment]
 
 The object file must be the build that was profiled (line numbers refer to its source)."""
 import csv,re,subprocess,sys,collections
@@ -29,7 +29,8 @@ for l in dis[start+1:]:
         continue
     m=re.match(r'\s+/\*([0-9a-f]{4,})\*/\s+(.*?);',l)
     if m: lines.append((int(m.group(1),16),cur,inl,m.group(2)))
-out=subprocess.run(f"ncu -i {rep} --page source --csv --kernel-name regex:{kern[:-1]}",shell=True,capture_output=True,text=True).stdout
+kre=sys.argv[4] if len(sys.argv)>4 else kern[:-1]
+out=subprocess.run(f"ncu -i {rep} --page source --csv --kernel-name regex:{kre}",shell=True,capture_output=True,text=True).stdout
 rows=list(csv.reader(out.splitlines()))
 for i,r in enumerate(rows):
     if '# Samples' in r: hdr=r; st=i+1; break
@@ -47,7 +48,6 @@ for r in data:
     if off in seen or off not in bymap: continue
     seen.add(off)
     ln,inl,txt=bymap[off]
-    if inl and len(sys.argv)>4: ln=inl
     n=int(r[iN]); ie=int(r[iI])
     agg[ln][0]+=n; agg[ln][1]+=ie; tot[0]+=n; tot[1]+=ie
 print('total samples',tot[0],'instr',tot[1],'n sass',len(data),len(lines))
