@@ -1774,13 +1774,15 @@ cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_pref
 
 cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, const unsigned long long *cand,
                            unsigned long long cand_cap, unsigned long long *tasks, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr,
-                           int num_sms, cudaStream_t s) {
+                           int num_sms, cudaStream_t s, bool tables_in_smem) {
     if (lib.fv.log2_bits == 0) return cudaSuccess;
     k_confirm<<<num_sms * 8, 256, 0, s>>>(text, total_bytes, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
     stage_mark("k_confirm");
     // per-warp shared-memory budget for the task's table: the largest verify table of the library, as long as
-    // 12 CTAs still fit an SM (the register limit of this kernel); larger tables are walked through L1
-    const uint32_t table_cap = lib.verify_table_cap;
+    // 12 CTAs still fit an SM (the register limit of this kernel); larger tables are walked through L1.  Only with
+    // one batch at a time on the device (tables_in_smem): the step alone gains 7 us, but with five batches in flight the
+    // 19 KiB per CTA cost 5 % of throughput (3.96 -> 3.77 TB/s) - the tails of several batches share the SMs then
+    const uint32_t table_cap = tables_in_smem ? lib.verify_table_cap : 0u;
     const size_t vsm = (size_t)kVerifyWarps * table_cap;
     if (vsm > 40 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsm);
@@ -1876,7 +1878,8 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
     stage_mark("join sort");
     // few, full CTAs: with several batches in flight every SM a small kernel sits on is an SM the next
     // batch's scan CTA (a whole SM each) has to wait for
-    unsigned fb = (unsigned)((key_cap + 511) / 512);
+    // (sized for the common case, <= kSmallSort keys; the kernel strides over more)
+    unsigned fb = (unsigned)((std::min<unsigned long long>(key_cap, (unsigned long long)kSmallSort) + 511) / 512);
     if (fb > (unsigned)num_sms * 2u) fb = (unsigned)num_sms * 2u;
     k_finalize<<<fb, 512, 0, s>>>(lib.blob, lib.h, keys, n_keys_dev, uniq, n_unique_dev, ev_cap, out, items, rs.results,
                                   reinterpret_cast<const EvAux *>(rs.aux), pt, rs.ctr, uniq_ready ? rank : nullptr);

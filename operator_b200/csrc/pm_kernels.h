@@ -92,7 +92,7 @@ cudaError_t launch_pods(const uint8_t *text, const unsigned long long *tile_pref
 // line -> verify DFA -> raw event).  `tasks` holds raw_cap u64.
 cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt,
                            const unsigned long long *cand, unsigned long long cand_cap, unsigned long long *tasks, unsigned long long *raw,
-                           unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);
+                           unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s, bool tables_in_smem = true);
 // wide / table_bytes: from the group's descriptor (GroupDesc.wide, nstates * stride * 2).
 cudaError_t launch_dfa_scan(const uint8_t *text, unsigned long long total_bytes, const DeviceLibrary &lib, PodTable pt, int group, bool wide,
                             size_t table_bytes, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr, int num_sms, cudaStream_t s);

@@ -823,7 +823,7 @@ int scan_async(pm_batch *b) {
         CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream2));
         CU(cudaEventRecord(w.pods_copied, w.stream2));
         CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.tasks.as<unsigned long long>(),
-                          w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), w.sms_post, w.stream));
+                          w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), w.sms_post, w.stream, /*tables_in_smem=*/d->depth == 1));
         w.launches += 1 + 2 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
         w.mark("k_verify");
         CU(cudaEventRecord(w.e[8], w.stream));
