@@ -44,12 +44,43 @@ def test_overflow_rerun_paths(tmp_path):
     assert r.returncode == 0 and "tiny-queues ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
 
 
-def test_many_raw_events_take_the_radix_sort_path(engine):
-    """More than 16384 raw events: the one-CTA sort declines, the host-sized radix sort runs."""
+def test_many_raw_events_take_the_merge_passes(engine):
+    """More than 16384 raw events: the shared-memory rank merge declines, the seven merge rounds of k_merge_all order
+    them on the device (up to 131072).  Every field against the oracle."""
     lib_json, wit, swit = synth.make_library(50)
     corpus, n_lines = synth.make_corpus(12 << 20, wit, swit, p_hit=0.25)
     res = check_parity(engine, lib_json, [corpus], expect_events=17000)
     assert res.n_events > 16384
+
+
+@pytest.mark.skipif(not pcre2_oracle.available(), reason="libpcre2-8 not loadable")
+def test_more_raw_events_than_the_device_sort_takes(engine):
+    """More than 131072 raw events: the host learns the count and the radix sort runs; the resolve stage is repeated
+    with result arrays of that size.  (line, pattern) pairs against the PCRE2 loop, every field of the head of the
+    log against the oracle."""
+    lib_json, wit, swit = synth.make_library(50)
+    engine.compile_library(lib_json).publish()
+    corpus, n_lines = synth.make_corpus(64 << 20, wit, swit, p_hit=0.4)
+    res = engine.scan([corpus])
+    assert res.n_events > 131072
+    pl = pcre2_oracle.Pcre2Library([p["primary_pattern"]["regex"] for p in lib_json["patterns"]])
+    starts, lens = pcre2_oracle.split(corpus)
+    ol, op, total = pcre2_oracle.scan(pl, corpus, starts, lens, threads=os.cpu_count() or 4)
+    pl.close()
+    assert total == ol.size
+    want = np.stack([ol + 1, op.astype(np.int64)], axis=1)
+    want = want[np.lexsort((want[:, 1], want[:, 0]))]
+    got = np.stack([res.line_no.astype(np.int64), res.pattern_index.astype(np.int64)], axis=1)
+    assert np.array_equal(got, want)
+    head = bytes(corpus[:60000])
+    head = head[:head.rfind(b"\n") + 1]
+    ev = oracle.analyze(head, oracle.load_library(lib_json))
+    n_head = len(oracle.split_lines(head))
+    got_head = [t for t in _got(res, 0) if t[0] <= n_head - 80]      # lines whose context window (after + STACK run) lies inside the head
+    want_head = [e for e in ev if e.line_no <= n_head - 80]
+    assert len(got_head) == len(want_head) > 50
+    for g, w in zip(got_head, want_head):
+        assert g[:8] == (w.line_no, w.pattern, w.line_start, w.line_len, w.ctx_first, w.ctx_last, w.ctx_start, w.ctx_end) and g[8] == w.score, (g, w)
 
 
 @pytest.mark.skipif(not pcre2_oracle.available(), reason="libpcre2-8 not loadable")
