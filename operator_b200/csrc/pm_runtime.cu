@@ -190,6 +190,14 @@ struct DriverApi {
 struct AdaptState {
     bool settled = false;
     int rounds = 0;
+    // Small batches (a service that gets one 1 MB pod log per request) say little each, so their candidate counts are
+    // added up: the decision is taken once 8 MiB of text have been seen, on whatever batch is staged then.
+    uint64_t seen_bytes = 0, seen_cand = 0;
+    // After the filter has settled the rate keeps being watched, 64 MiB at a time: logs whose vocabulary has drifted
+    // (a new release, another tenant) open the selection again, at most kMaxReopen times per library and device.
+    double settled_rate = 0.0;
+    uint64_t watch_bytes = 0, watch_cand = 0;
+    int reopened = 0;
     void *dev_filter = nullptr;     // rebuilt filter sections (one allocation)
     std::vector<void *> retired;    // earlier ones: a batch in flight may still read them; freed with the library
 };
@@ -624,14 +632,35 @@ int maybe_adapt(pm_library *l, DevWork &w) {
     if (!adapt_lock.owns_lock()) return PM_OK;   // another batch is at it
     AdaptState &st = l->adapt[slot];
     DeviceLibrary &dl = l->dev[slot];
-    if (st.settled || !dl.fv.log2_bits || w.total < (8u << 20)) return PM_OK;   // small batches say nothing about rates
-    const double words = (double)w.total / 4.0;
-    const double fill = (double)dl.fv.n_grams / (double)(1ull << dl.fv.log2_bits);
-    const double rate = (double)w.n_cand / words;
+    if (!dl.fv.log2_bits) return PM_OK;
     const bool debug = getenv("PM_DEBUG") != nullptr;
-    if (debug) fprintf(stderr, "[pm] filter: %llu candidates, rate %.5f, fill %.5f, round %d\n", (unsigned long long)w.n_cand, rate, fill, st.rounds);
+    constexpr int kMaxReopen = 4;
+    if (st.settled) {   // keep watching the rate
+        st.watch_bytes += w.total;
+        st.watch_cand += w.n_cand;
+        if (st.watch_bytes < (64ull << 20)) return PM_OK;
+        const double now = (double)st.watch_cand / ((double)st.watch_bytes / 4.0);
+        st.watch_bytes = st.watch_cand = 0;
+        if (now <= 4.0 * st.settled_rate + 1e-4 || st.reopened >= kMaxReopen) return PM_OK;
+        if (debug) fprintf(stderr, "[pm] filter: rate %.5f against %.5f when it settled: selecting windows again\n", now, st.settled_rate);
+        st.settled = false;
+        st.rounds = 0;
+        st.reopened++;
+        st.seen_bytes = st.seen_cand = 0;
+        return PM_OK;   // the next batches decide
+    }
+    st.seen_bytes += w.total;
+    st.seen_cand += w.n_cand;
+    if (st.seen_bytes < (8ull << 20) || w.total < (256u << 10)) return PM_OK;   // not enough text yet / too small a sample to profile
+    const double words = (double)st.seen_bytes / 4.0;
+    const double fill = (double)dl.fv.n_grams / (double)(1ull << dl.fv.log2_bits);
+    const double rate = (double)st.seen_cand / words;
+    if (debug) fprintf(stderr, "[pm] filter: %llu candidates in %llu bytes, rate %.5f, fill %.5f, round %d\n", (unsigned long long)st.seen_cand,
+                       (unsigned long long)st.seen_bytes, rate, fill, st.rounds);
+    st.seen_bytes = st.seen_cand = 0;
     if (rate <= 3.0 * fill + 2e-5 || st.rounds >= 2) {
         st.settled = true;
+        st.settled_rate = rate;
         return PM_OK;
     }
     st.rounds++;

@@ -280,3 +280,26 @@ def test_device_generator_is_byte_identical_and_device_pods_scan_alike(engine):
     assert got.pod_n_lines.tolist() == want.pod_n_lines.tolist()
     for name in ("pod_index", "pattern_index", "line_no", "line_start", "line_len", "ctx_first_line", "ctx_last_line", "ctx_start", "ctx_end", "score"):
         assert np.array_equal(getattr(got, name), getattr(want, name)), name
+
+
+def test_filter_adapts_over_many_small_requests():
+    """A service sees one ~1 MB pod log per request: no single batch says enough about gram frequencies, so the
+    candidate counts of successive batches are added up and the profile-guided window selection runs once 8 MiB
+    have gone by (on the batch staged then).  Results never change; the candidate count of a request drops."""
+    from operator_b200 import Engine
+    lib_json, wit, swit = synth.make_library(500)
+    eng = Engine(1)
+    try:
+        eng.compile_library(lib_json).publish()
+        pods = [synth.make_corpus(1400 << 10, wit, swit, p_hit=1e-3, first_line=k << 30)[0].copy() for k in range(16)]
+        cand, events = [], []
+        for p in pods:
+            r = eng.scan([p])
+            cand.append(r.n_candidates)
+            events.append(r.n_events)
+        again = [eng.scan([p]) for p in pods[:3]]
+        assert [a.n_events for a in again] == events[:3]            # same answers before and after the re-selection
+        assert min(cand[:4]) > 2000                                 # static model: "thre", "conn", ... are everywhere in this text
+        assert max(cand[-4:]) * 5 < min(cand[:4]), cand             # after ~8 MiB the windows were re-selected
+    finally:
+        eng.close()
