@@ -381,6 +381,28 @@ def leg_hit_sweep(args, eng, torch, dist, lib_json, wit, swit, sync_all, peak):
     return out
 
 
+def leg_short_literal_library(args, eng, torch, dist, sync_all, peak):
+    """The 500-pattern library with every tenth primary replaced by a regex whose required literal has 5 or 6 bytes
+    (\\bEPIPE\\b, (?i)errno \\d+, [Cc]ache (evicted|flushed), ...): the library compiles to filter granule 2 - k_scan_half
+    tests the word at every even offset, twice the lookups - and no pattern needs the combined DFA."""
+    from operator_b200 import synth
+    lj, w, sw = synth.make_mixed_library(args.patterns, min_literal=5)
+    rep = eng.compile_library(lj).publish().report
+    t = torch.empty(args.corpus_bytes, dtype=torch.uint8, device="cuda")
+    n, lines = synth.make_corpus_device(t.data_ptr(), args.corpus_bytes, w, sw, p_hit=P_HIT, first_line=79 << 36)
+    one, piped, stats = measure_corpus(eng, torch, dist, t, n, max(3, min(args.steps, 10)), args.depth, sync_all)
+    del t
+    torch.cuda.empty_cache()
+    row = {"workload": "config-2 corpus vs the 500-pattern library with 10 % primaries of 5-6 byte literals (filter granule 2, no DFA pass)",
+           "library": {k: rep[k] for k in ("n_patterns", "n_filtered", "n_dfa_scanned", "dfa_groups", "n_grams", "filter_log2_bits", "blob_bytes")},
+           "k_scan_half_gbs": n / (one["k_scan_ms"] * 1e-3) / 1e9, "k_scan_half_frac_of_measured_hbm": n / (one["k_scan_ms"] * 1e-3) / 1e9 / peak}
+    row.update(stats)
+    row["one_batch_at_a_time"] = one
+    row["pipelined"] = piped
+    row["frac_of_measured_hbm"] = (piped or one)["gbs"] / peak
+    return row
+
+
 def leg_mixed_library(args, eng, torch, dist, sync_all, peak):
     """The 500-pattern library with every tenth primary replaced by a short-literal / class-led regex
     (\\bOOM\\b, exit code 137\\b, (?i)errno \\d+, [Cc]ache (evicted|flushed), ...): what has no 7-byte literal goes to
@@ -694,10 +716,11 @@ def main():
         eng.compile_library(lib_json).publish()
 
     # ---- hit density / near misses, and the mixed library that reaches the combined DFA (N = 1)
-    hit_sweep = mixed = None
+    hit_sweep = mixed = short5 = None
     if world == 1 and not args.no_sweep:
         hit_sweep = leg_hit_sweep(args, eng, torch, dist, lib_json, wit, swit, sync_all, peak_hbm()[0])
         mixed = leg_mixed_library(args, eng, torch, dist, sync_all, peak_hbm()[0])
+        short5 = leg_short_literal_library(args, eng, torch, dist, sync_all, peak_hbm()[0])
         eng.compile_library(lib_json).publish()
 
     # ---- BASELINE configs 3 and 5 (every rank takes part)
@@ -769,6 +792,7 @@ def main():
             "config1_latency": latency,
             "hit_sweep": hit_sweep,
             "mixed_library": mixed,
+            "short_literal_library": short5,
             "config3_crash_storm": cfg3,
             "config5_fixed_corpus": cfg5,
             "single_context": single,

@@ -24,9 +24,15 @@
 namespace pm {
 
 constexpr uint32_t kBlobMagic = 0x424C4D50u;   // "PMLB"
-constexpr uint32_t kBlobVersion = 8;
+constexpr uint32_t kBlobVersion = 9;
 constexpr int kGramLen = 4;        // bytes per gram = one aligned 32-bit text word
 constexpr int kMinLiteral = 7;     // any 7-byte window covers one aligned 4-byte word
+// Granule of the gram filter: the text offsets whose 4-byte word k_scan tests are the multiples of it.
+//   4: aligned words, one lookup per 4 bytes; a literal needs a 7-byte window (4 grams, one per alignment);
+//   2: also the words that straddle two aligned ones, one lookup per 2 bytes; a 5-byte window is enough (2 grams).
+// A library compiles to granule 2 exactly when that takes every pattern off the combined DFA (pm_library.cc).
+constexpr int kMinLiteralHalf = 5;
+inline int window_bytes(int granule) { return kGramLen + granule - 1; }
 constexpr uint32_t kGramEmpty = 0xFFFFFFFFu;   // 0xFF never occurs in valid UTF-8
 constexpr int kStackMax = 50;      // SPEC.md section 6
 constexpr int kMaxSecondary = 8;
@@ -43,6 +49,8 @@ struct BlobHeader {
     uint64_t off_units, off_classmaps, off_tables, off_patterns, off_secondaries, off_groups;
     uint64_t off_group_accept;   // u32 pool: per-group accept index + lists
     uint64_t total_bytes;
+    uint32_t filter_granule;     // 4 or 2 (see kMinLiteralHalf)
+    uint32_t pad_;
 };
 
 struct Probe {

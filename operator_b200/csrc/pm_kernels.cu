@@ -88,14 +88,15 @@ struct ConfirmParams {
 // One filter hit, the whole warp: (16-byte group, mask of its 4 aligned words) -> exact gram lookup
 // (warp-uniform) -> every lane takes one probe of the gram's probe list and compares its literal
 // -> (position, pattern) verify tasks.
-__device__ __forceinline__ void confirm_candidate(const ConfirmParams &cp, ScanCounters *ctr, unsigned long long group, uint32_t m4) {
+__device__ __forceinline__ void confirm_candidate(const ConfirmParams &cp, ScanCounters *ctr, unsigned long long group, uint32_t m4, uint32_t step) {
     const int lane = threadIdx.x & 31;
     const uint32_t cap_mask = (1u << cp.log2_cap) - 1u;
     while (m4) {
         const int k = __ffs(m4) - 1;
         m4 &= m4 - 1;
-        const unsigned long long p = group * 16 + k * 4;
-        uint32_t g = *reinterpret_cast<const uint32_t *>(cp.text + p);
+        const unsigned long long p = group * 16 + k * step;
+        // (at granule 2 the word may sit at an offset that is only 2-aligned: two aligned halves)
+        uint32_t g = (uint32_t)*reinterpret_cast<const unsigned short *>(cp.text + p) | ((uint32_t)*reinterpret_cast<const unsigned short *>(cp.text + p + 2) << 16);
         if (cp.fold) g |= 0x20202020u;
         uint32_t slot = gram_table_slot(g, cp.log2_cap);
         uint32_t key;
@@ -306,6 +307,141 @@ k_scan(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *
         if (t >= n_tiles) break;
         load_tile(t + n_warps, va);
         process_tile(t, vb);
+        t += n_warps;
+    }
+    if (qn > 0) {
+        unsigned long long at = 0;
+        if (lane == 0) at = atomicAdd(&ctr->n_cand, (unsigned long long)qn);
+        at = __shfl_sync(FULL, at, 0);
+        if (at + qn <= cand_cap) {
+            if (lane < qn) cand[at + lane] = wq[lane];
+            if (lane + 32 < qn) cand[at + lane + 32] = wq[lane + 32];
+        } else if (lane == 0) {
+            ctr->cand_overflow = 1;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ k_scan_half
+// Granule 2 (pm_blob.h): the filter also tests the words that straddle two aligned ones, i.e. the 4-byte word at
+// every EVEN text offset, so that a required literal of 5 bytes is enough (it always contains a word that starts
+// at an even offset).  Same structure as k_scan - a kernel of its own so that k_scan's loop, which sits exactly at
+// 64 registers, is not touched.  Per aligned word one funnel shift, one more hash and one more bitmap lookup; the
+// word behind a lane's 16 bytes comes from the next lane (the last lane: from lane 0 of the next 512-byte row, or
+// from the tile behind).  Hits leave as (16-byte group << 8) | mask of the 8 even offsets.
+template <bool FOLD>
+__device__ __forceinline__ uint32_t filter_word(uint32_t w, const ScanConsts &k) {
+    const uint32_t g = FOLD ? (w | k.c_20) : w;
+    const uint32_t h = g * k.mult;
+    const uint32_t idx = mad_hi(h, k.idx_mul, 0u);
+    const uint32_t word = lds_u32(mad_lo(idx, k.four, k.bm_base));
+    return shr_wrap(word, h);
+}
+
+#ifndef PM_HALF_THREADS
+#define PM_HALF_THREADS 768
+#endif
+constexpr int kHalfThreads = PM_HALF_THREADS;
+
+template <int BITS, bool FOLD>
+__global__ void __launch_bounds__(kHalfThreads, 1)
+k_scan_half(const uint4 *__restrict__ text, unsigned long long n_tiles, const uint4 *__restrict__ bitmap_g, const uint4 *__restrict__ bitmap2_g,
+            uint32_t bits2, uint32_t *__restrict__ tile_nl, unsigned long long *__restrict__ cand, unsigned long long cand_cap,
+            ScanCounters *__restrict__ ctr, const ScanConsts kc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int kBitmapWords = (1 << BITS) / 32;
+    uint32_t *bm = reinterpret_cast<uint32_t *>(smem_raw);
+    const int bm2_words = (1 << bits2) / 32;
+    uint32_t *bm2 = bm + kBitmapWords;
+    unsigned long long *queues = reinterpret_cast<unsigned long long *>(smem_raw + (size_t)(kBitmapWords + bm2_words) * 4);
+    const uint32_t shift2 = 32 - bits2;
+    for (int i = threadIdx.x; i < kBitmapWords / 4; i += blockDim.x) reinterpret_cast<uint4 *>(bm)[i] = bitmap_g[i];
+    for (int i = threadIdx.x; i < bm2_words / 4; i += blockDim.x) reinterpret_cast<uint4 *>(bm2)[i] = bitmap2_g[i];
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long *wq = queues + warp * kQueue;
+    int qn = 0;
+    const unsigned long long n_warps = (unsigned long long)gridDim.x * (kHalfThreads / 32);
+    const unsigned lt = lanemask_lt();
+    const unsigned long long pol = l2_evict_first_policy();
+    ScanConsts k = kc;
+    k.bm_base = (uint32_t)__cvta_generic_to_shared(bm);
+    const uint32_t *text_w = reinterpret_cast<const uint32_t *>(text);
+
+    auto process_tile = [&](unsigned long long tt, uint4 (&v)[4], uint32_t behind) {   // behind: first word of the tile after this one
+        uint32_t nz_acc = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            // the word that follows this lane's 16 bytes
+            const uint32_t from_next_lane = __shfl_down_sync(FULL, v[j].x, 1);
+            const uint32_t from_next_row = j < 3 ? __shfl_sync(FULL, v[j < 3 ? j + 1 : 3].x, 0) : behind;
+            const uint32_t nx = lane == 31 ? from_next_row : from_next_lane;
+            const uint32_t t0 = scan_word<FOLD>(v[j].x, k, nz_acc), t1 = scan_word<FOLD>(v[j].y, k, nz_acc);
+            const uint32_t t2 = scan_word<FOLD>(v[j].z, k, nz_acc), t3 = scan_word<FOLD>(v[j].w, k, nz_acc);
+            const uint32_t s0 = filter_word<FOLD>(__funnelshift_r(v[j].x, v[j].y, 16), k), s1 = filter_word<FOLD>(__funnelshift_r(v[j].y, v[j].z, 16), k);
+            const uint32_t s2 = filter_word<FOLD>(__funnelshift_r(v[j].z, v[j].w, 16), k), s3 = filter_word<FOLD>(__funnelshift_r(v[j].w, nx, 16), k);
+            const uint32_t any = lop3_or_and(lop3_or3(t0, t1, t2) | lop3_or3(s0, s1, s2), t3 | s3, k.one);
+            unsigned b = __ballot_sync(FULL, any != 0);
+            if (b) {   // warp-uniform, rare: second-level bitmap, then the queue
+                uint32_t m8 = (t0 & 1u) | ((s0 & 1u) << 1) | ((t1 & 1u) << 2) | ((s1 & 1u) << 3) | ((t2 & 1u) << 4) | ((s2 & 1u) << 5) | ((t3 & 1u) << 6) |
+                              ((s3 & 1u) << 7);
+                if (m8) {
+                    const uint32_t w8[8] = {v[j].x, __funnelshift_r(v[j].x, v[j].y, 16), v[j].y, __funnelshift_r(v[j].y, v[j].z, 16),
+                                            v[j].z, __funnelshift_r(v[j].z, v[j].w, 16), v[j].w, __funnelshift_r(v[j].w, nx, 16)};
+#pragma unroll
+                    for (int q = 0; q < 8; q++)
+                        if (m8 & (1u << q)) {
+                            uint32_t g = FOLD ? (w8[q] | 0x20202020u) : w8[q];
+                            uint32_t bit2 = (g * 0xC2B2AE3Du) >> shift2;
+                            if (!((bm2[bit2 >> 5] >> (bit2 & 31u)) & 1u)) m8 &= ~(1u << q);
+                        }
+                }
+                b = __ballot_sync(FULL, m8 != 0);
+                if (b) {
+                    if (m8) wq[qn + __popc(b & lt)] = ((tt * (kTileBytes / 16) + j * 32 + lane) << 8) | m8;
+                    qn += __popc(b);
+                    __syncwarp();
+                    if (qn >= 32) {
+                        unsigned long long at = 0;
+                        if (lane == 0) at = atomicAdd(&ctr->n_cand, 32ull);
+                        at = __shfl_sync(FULL, at, 0);
+                        if (at + 32 <= cand_cap)
+                            cand[at + lane] = wq[lane];
+                        else if (lane == 0)
+                            ctr->cand_overflow = 1;
+                        unsigned long long carry = (lane + 32 < qn) ? wq[lane + 32] : 0ull;
+                        __syncwarp();
+                        qn -= 32;
+                        if (lane < qn) wq[lane] = carry;
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+        const uint32_t nz = nz_acc >> 7;
+        uint32_t nl = __reduce_add_sync(FULL, 64u - nz);
+        if (lane == 0) tile_nl[tt] = nl;
+    };
+    unsigned long long t = (unsigned long long)blockIdx.x * (kHalfThreads / 32) + warp;
+    uint4 va[4], vb[4];
+    uint32_t na = 0x0A0A0A0Au, nb_ = 0x0A0A0A0Au;
+    auto load_tile = [&](unsigned long long tt, uint4 (&dst)[4], uint32_t &behind) {
+        const unsigned long long tc = tt < n_tiles ? tt : n_tiles - 1;   // past the end: harmless re-load
+        const uint4 *nb = text + tc * (kTileBytes / 16) + lane;
+#pragma unroll
+        for (int j = 0; j < 4; j++) dst[j] = ld_stream16_ef(nb + j * 32, pol);
+        // (only the last lane uses it; behind the last tile there is nothing: the buffer ends in '\n' padding)
+        behind = (lane == 31 && tc + 1 < n_tiles) ? __ldg(text_w + (tc + 1) * (kTileBytes / 4)) : 0x0A0A0A0Au;
+    };
+    if (t < n_tiles) load_tile(t, va, na);
+    while (t < n_tiles) {
+        load_tile(t + n_warps, vb, nb_);
+        process_tile(t, va, na);
+        t += n_warps;
+        if (t >= n_tiles) break;
+        load_tile(t + n_warps, va, na);
+        process_tile(t, vb, nb_);
         t += n_warps;
     }
     if (qn > 0) {
@@ -554,9 +690,13 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
     ConfirmParams cp;
     cp.text = text, cp.total = total, cp.gkeys = fv.gkeys, cp.gfirst = fv.gfirst, cp.gcount = fv.gcount, cp.probes = fv.probes, cp.litpool = fv.litpool;
     cp.log2_cap = fv.log2_cap, cp.fold = fv.fold, cp.tasks = tasks, cp.task_cap = task_cap;
+    const bool half = fv.granule == 2;   // (group << 8) | 8 even offsets, else (group << 4) | 4 aligned words
     for (unsigned long long i = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += n_warps) {
         const unsigned long long e = cand[i];
-        confirm_candidate(cp, ctr, e >> 4, (uint32_t)(e & 15u));
+        if (half)
+            confirm_candidate(cp, ctr, e >> 8, (uint32_t)(e & 255u), 2u);
+        else
+            confirm_candidate(cp, ctr, e >> 4, (uint32_t)(e & 15u), 4u);
     }
 }
 
@@ -1721,6 +1861,35 @@ cudaError_t launch_scan_one(const uint8_t *text, unsigned long long n_tiles, con
     return cudaGetLastError();
 }
 
+template <int BITS, bool FOLD>
+cudaError_t launch_scan_half_one(const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, const uint4 *bitmap2, uint32_t bits2, uint32_t *tile_nl,
+                                 unsigned long long *cand, unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    const size_t smem = (size_t)(1 << BITS) / 8 + (size_t)(1u << bits2) / 8 + (size_t)(kHalfThreads / 32) * kQueue * 8;
+    ScanConsts kc;
+    kc.c_nl = 0x0A0A0A0Au;
+    kc.c_7f = 0x7F7F7F7Fu;
+    kc.c_80 = 0x80808080u;
+    kc.c_20 = 0x20202020u;
+    kc.one = 1u;
+    kc.four = 4u;
+    kc.two25 = 0x01010101u;
+    kc.idx_mul = 1u << (BITS - 5);
+    kc.mult = kFilterMult0;
+    kc.bm_base = 0;
+    cudaError_t e = cudaFuncSetAttribute(k_scan_half<BITS, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_scan_half<BITS, FOLD><<<num_sms, kHalfThreads, smem, s>>>(reinterpret_cast<const uint4 *>(text), n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr,
+                                                               kc);
+    return cudaGetLastError();
+}
+
+template <int BITS>
+cudaError_t launch_scan_half_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, const uint4 *bitmap2, uint32_t bits2,
+                                  uint32_t *tile_nl, unsigned long long *cand, unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
+    return fold ? launch_scan_half_one<BITS, true>(text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s)
+                : launch_scan_half_one<BITS, false>(text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+}
+
 template <int BITS>
 cudaError_t launch_scan_bits(bool fold, const uint8_t *text, unsigned long long n_tiles, const uint4 *bitmap, const uint4 *bitmap2, uint32_t bits2,
                              uint32_t *tile_nl, unsigned long long *cand, unsigned long long cand_cap, ScanCounters *ctr, int num_sms, cudaStream_t s) {
@@ -1746,6 +1915,17 @@ cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const D
     const uint4 *bitmap = reinterpret_cast<const uint4 *>(fv.bitmap), *bitmap2 = reinterpret_cast<const uint4 *>(fv.bitmap2);
     const uint32_t bits2 = fv.log2_bits2;
     const bool fold = fv.fold != 0;
+    if (fv.granule == 2) {   // every even offset is tested (5-byte literals)
+        switch (fv.log2_bits) {
+            case 15: return launch_scan_half_bits<15>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+            case 16: return launch_scan_half_bits<16>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+            case 17: return launch_scan_half_bits<17>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+            case 18: return launch_scan_half_bits<18>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+            case 19: return launch_scan_half_bits<19>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+            case 20: return launch_scan_half_bits<20>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
+            default: return cudaErrorInvalidValue;
+        }
+    }
     switch (fv.log2_bits) {
         case 15: return launch_scan_bits<15>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);
         case 16: return launch_scan_bits<16>(fold, text, n_tiles, bitmap, bitmap2, bits2, tile_nl, cand, cand_cap, ctr, num_sms, s);

@@ -7,7 +7,7 @@
 //               Every line of every pod is therefore delimited by '\n' on both sides.
 //   tile_nl     u32 per 2 KiB tile: number of '\n' bytes in the tile          (k_scan)
 //   tile_prefix u64 per tile: '\n' bytes before the tile                      (k_prefix_*)
-//   cand        u64 per filter hit: (16-byte group index << 4) | word mask    (k_scan)
+//   cand        u64 per filter hit: (16-byte group index << 8) | mask of the even offsets whose word hit   (k_scan)
 //   raw events  u64 key = (line_start << 24) | pattern                        (k_confirm, k_dfa_scan)
 #pragma once
 #include <cuda_runtime.h>
@@ -38,6 +38,7 @@ struct FilterView {
     const Probe *probes = nullptr;
     const uint8_t *litpool = nullptr;
     uint32_t log2_bits = 0, log2_bits2 = 0, log2_cap = 0, fold = 0, n_grams = 0;
+    uint32_t granule = 4;   // 4: k_scan tests the aligned words; 2: every even offset (pm_blob.h)
 };
 
 struct DeviceLibrary {

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 
@@ -61,14 +62,14 @@ bool num_of(const JsonValue *v, double &out) {
 // Cost of sampling the 7-byte window at `o`: expected filter hits per text word (lower is
 // better); windows that touch a case-insensitive position are pushed back because they force
 // the whole library into fold mode.
-double window_cost(const Literal &l, size_t o) {
+double window_cost(const Literal &l, size_t o, int granule) {
     double cost = 0;
-    for (int k = 0; k < 4; k++) {
+    for (int k = 0; k < granule; k++) {
         int bits = 0;
         for (int j = 0; j < kGramLen; j++) bits += byte_rarity(l.bytes[o + k + j]);
         cost += std::ldexp(1.0, -bits);
     }
-    for (size_t j = o; j < o + kMinLiteral; j++)
+    for (size_t j = o; j < o + (size_t)window_bytes(granule); j++)
         if (l.mask[j]) cost += 1.0;
     return cost;
 }
@@ -189,8 +190,10 @@ bool build_scan_table(const Dfa &d, size_t max_bytes, ScanTable &out) {
     return true;
 }
 
-void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mode, const GramCostFn *cost, FilterBuild &out) {
+void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mode, const GramCostFn *cost, int granule, FilterBuild &out) {
     out = FilterBuild();
+    out.granule = granule;
+    const size_t win = (size_t)window_bytes(granule);
     struct Chosen {
         int pattern;
         const Literal *lit;
@@ -202,21 +205,21 @@ void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mo
         for (auto &l : literals[i]) {
             size_t best_o = 0;
             double best = 1e300;
-            for (size_t o = 0; o + kMinLiteral <= l.bytes.size(); o++) {
+            for (size_t o = 0; o + win <= l.bytes.size(); o++) {
                 bool masked = false;
-                for (size_t j = o; j < o + kMinLiteral; j++) masked |= l.mask[j] != 0;
+                for (size_t j = o; j < o + win; j++) masked |= l.mask[j] != 0;
                 double c;
                 if (cost) {
-                    c = 1e-12 * window_cost(l, o);   // static model only breaks ties
-                    for (int k = 0; k < 4; k++) c += (*cost)(gram_at(l, o + k, fold_mode == 1));
+                    c = 1e-12 * window_cost(l, o, granule);   // static model only breaks ties
+                    for (int k = 0; k < granule; k++) c += (*cost)(gram_at(l, o + k, fold_mode == 1));
                     if (masked && fold_mode == 0) c = 1e299;   // would need fold mode, which is fixed
                 } else {
-                    c = window_cost(l, o);   // penalises masked windows (they force fold mode)
+                    c = window_cost(l, o, granule);   // penalises masked windows (they force fold mode)
                     if (masked && fold_mode == 0) c = 1e299;
                 }
                 if (c < best) best = c, best_o = o;
             }
-            for (size_t j = best_o; j < best_o + kMinLiteral; j++)
+            for (size_t j = best_o; j < best_o + win; j++)
                 if (l.mask[j]) fold = true;
             chosen.push_back({(int)i, &l, best_o});
         }
@@ -231,7 +234,7 @@ void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mo
         while (out.litpool.size() % 4) out.litpool.push_back(0xFF);
         out.litpool.insert(out.litpool.end(), c.lit->mask.begin(), c.lit->mask.end());
         while (out.litpool.size() % 4) out.litpool.push_back(0xFF);
-        for (int k = 0; k < 4; k++) {
+        for (int k = 0; k < granule; k++) {
             Probe pr;
             pr.pattern = (uint32_t)c.pattern;
             pr.lit_off = lit_off;
@@ -408,14 +411,26 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         compile_unit(kStackRegex, -1, -1, "<stack>", units.back(), nullptr);
         context_units.push_back(stack_unit);
 
-        // ---- tiering: literal-gram filter where a 7+ byte literal is required, DFA otherwise
+        // ---- tiering: literal-gram filter where a long enough literal is required, DFA otherwise.  "Long enough" is 7
+        //      bytes with the filter testing aligned words; if testing every even offset as well (5 bytes are enough then,
+        //      k_scan does twice the lookups) takes EVERY pattern off the combined DFA, the library is compiled that way: a
+        //      second, table-walking pass over the text costs five times what the extra lookups do.
         out.literals.resize(P);
         std::vector<int> tier2;
+        std::vector<std::vector<Literal>> lits_of(P);
+        std::vector<int> quality_of(P, 0);
+        int shortest = 1 << 30;
         for (int i = 0; i < P; i++) {
-            int q = 0;
-            std::vector<Literal> lits = required_literals(*asts[i], &q);
-            if (q >= kMinLiteral) {
-                out.literals[i] = std::move(lits);
+            lits_of[i] = required_literals(*asts[i], &quality_of[i]);
+            shortest = std::min(shortest, quality_of[i]);
+        }
+        static const bool allow_half = getenv("PM_FILTER_GRANULE4") == nullptr;
+        const int granule = (allow_half && shortest >= kMinLiteralHalf && shortest < kMinLiteral) ? 2 : 4;
+        const int min_literal = granule == 2 ? kMinLiteralHalf : kMinLiteral;
+        out.granule = granule;
+        for (int i = 0; i < P; i++) {
+            if (quality_of[i] >= min_literal) {
+                out.literals[i] = std::move(lits_of[i]);
                 pdesc[i].tier = 1;
             } else {
                 pdesc[i].tier = 2;
@@ -427,7 +442,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         // ---- gram selection (static byte-rarity model; the runtime may re-select from measured
         //      gram frequencies, see build_filter / pm_runtime.cu)
         FilterBuild fb;
-        build_filter(out.literals, /*fold_mode=*/-1, nullptr, fb);
+        build_filter(out.literals, /*fold_mode=*/-1, nullptr, granule, fb);
         const bool fold = fb.fold;
         const uint32_t n_grams = fb.n_grams, n_probes = fb.n_probes, log2_bits = fb.log2_bits, log2_cap = fb.log2_cap;
         std::vector<uint32_t> &bitmap = fb.bitmap, &gkeys = fb.gkeys, &gfirst = fb.gfirst, &gcount = fb.gcount;
@@ -535,6 +550,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         h.filter_log2_bits = log2_bits;
         h.filter_log2_bits2 = fb.log2_bits2;
         h.filter_fold = fold;
+        h.filter_granule = (uint32_t)granule;
         h.gram_log2_cap = log2_cap;
         h.n_grams = n_grams;
         h.n_probes = n_probes;
@@ -735,6 +751,7 @@ int deserialize_library(const uint8_t *data, size_t n, CompiledLibrary &lib, std
         err = "device blob has another layout version";
         return PM_E_UNSUPPORTED;
     }
+    lib.granule = h->filter_granule == 2 ? 2 : 4;
     const uint32_t np = r.u32();
     for (uint32_t i = 0; i < np && r.ok; i++) {
         PatternInfo p;

@@ -26,6 +26,7 @@ struct PatternInfo {
 // runtime rebuilds it when it has measured which grams are frequent in the actual logs.
 struct FilterBuild {
     uint32_t log2_bits = 0, log2_bits2 = 0, log2_cap = 4, n_grams = 0, n_probes = 0;
+    int granule = 4;
     bool fold = false;
     std::vector<uint32_t> bitmap, bitmap2, gkeys, gfirst, gcount;
     std::vector<Probe> probes;
@@ -34,8 +35,8 @@ struct FilterBuild {
 using GramCostFn = std::function<double(uint32_t gram)>;   // expected hits per aligned text word
 
 // fold_mode: -1 decide (fold iff a chosen window has a case-insensitive position), 0/1 fixed.
-// cost == nullptr: static byte-rarity model.
-void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mode, const GramCostFn *cost, FilterBuild &out);
+// cost == nullptr: static byte-rarity model.  granule: 4 (7-byte windows, 4 grams each) or 2 (5-byte windows, 2 grams).
+void build_filter(const std::vector<std::vector<Literal>> &literals, int fold_mode, const GramCostFn *cost, int granule, FilterBuild &out);
 // Every distinct 4-byte gram of every literal (folded when `fold`), sorted.
 void collect_all_grams(const std::vector<std::vector<Literal>> &literals, bool fold, std::vector<uint32_t> &grams);
 
@@ -57,6 +58,7 @@ struct CompiledLibrary {
     std::vector<Dfa> unit_dfas;                      // index = unit id
     std::vector<std::vector<Literal>> literals;      // per pattern (empty for tier 2)
     bool fold = false;
+    int granule = 4;                                 // of the gram filter (pm_blob.h)
     std::vector<Dfa> group_dfas;
     std::vector<ScanTable> group_scan;
     std::vector<std::vector<int>> group_patterns;    // unit id in a group -> pattern index

@@ -653,7 +653,8 @@ int maybe_adapt(pm_library *l, DevWork &w) {
     st.seen_cand += w.n_cand;
     if (st.seen_bytes < (8ull << 20) || w.total < (256u << 10)) return PM_OK;   // not enough text yet / too small a sample to profile
     const double words = (double)st.seen_bytes / 4.0;
-    const double fill = (double)dl.fv.n_grams / (double)(1ull << dl.fv.log2_bits);
+    // what a filter whose grams are absent from the text would still let through: a word must collide in both bitmaps
+    const double fill = (double)dl.fv.n_grams / (double)(1ull << dl.fv.log2_bits) * (double)dl.fv.n_grams / (double)(1ull << dl.fv.log2_bits2);
     const double rate = (double)st.seen_cand / words;
     if (debug) fprintf(stderr, "[pm] filter: %llu candidates in %llu bytes, rate %.5f, fill %.5f, round %d\n", (unsigned long long)st.seen_cand,
                        (unsigned long long)st.seen_bytes, rate, fill, st.rounds);
@@ -701,7 +702,7 @@ int maybe_adapt(pm_library *l, DevWork &w) {
         return (c + 0.25) / sample_words;
     };
     FilterBuild fb;
-    build_filter(l->lib.literals, fold ? 1 : 0, &cost, fb);
+    build_filter(l->lib.literals, fold ? 1 : 0, &cost, l->lib.granule, fb);
     // ---- 3. upload the rebuilt sections and switch the view
     auto a16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
     size_t o_bm = 0, o_b2 = a16(o_bm + fb.bitmap.size() * 4), o_k = a16(o_b2 + fb.bitmap2.size() * 4), o_f = a16(o_k + fb.gkeys.size() * 4), o_c = a16(o_f + fb.gfirst.size() * 4);
@@ -1314,6 +1315,7 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
             fv.log2_bits = bh.filter_log2_bits;
             fv.log2_cap = bh.gram_log2_cap;
             fv.fold = bh.filter_fold;
+            fv.granule = bh.filter_granule == 2 ? 2u : 4u;
             fv.n_grams = bh.n_grams;
             {   // largest context / proximity window of the library -> shared-memory slots of k_plan
                 const uint8_t *hb = l->lib.blob.data();

@@ -187,14 +187,20 @@ SHORT_PRIMARIES = (
 )
 
 
-def make_mixed_library(n_patterns: int, fraction: float = 0.1, seed: int = LIB_SEED) -> Tuple[dict, List[str], List[Optional[str]]]:
-    """make_library with every (1/fraction)-th primary replaced by a short-literal / class-led regex."""
+def make_mixed_library(n_patterns: int, fraction: float = 0.1, seed: int = LIB_SEED, min_literal: int = 0) -> Tuple[dict, List[str], List[Optional[str]]]:
+    """make_library with every (1/fraction)-th primary replaced by a short-literal / class-led regex.
+    min_literal: only templates whose required literal has at least that many bytes (5: what the gram filter can
+    still serve by testing every even offset; 0: all, including the 3-byte codes that need the combined DFA)."""
     lib, wit, swit = make_library(n_patterns, seed, "synthetic-mixed")
     step = max(1, int(round(1.0 / fraction)))
+    templates = SHORT_PRIMARIES
+    if min_literal >= 5:
+        short = set("\\b%s\\b" % c for c in SHORT_CODES if len(c) < 5) | {"\\bERR-\\d{3,4}\\b", "\\bQK\\d{3,4}\\b", "\\bHHH\\d{3,4}\\b", "\\btimed? ?out\\b"}
+        templates = [t for t in SHORT_PRIMARIES if t[0] not in short]
     k = 0
     for i in range(0, n_patterns, step):
-        rx, w = SHORT_PRIMARIES[k % len(SHORT_PRIMARIES)]
-        if k >= len(SHORT_PRIMARIES):      # more slots than templates: make the regex distinct
+        rx, w = templates[k % len(templates)]
+        if k >= len(templates):            # more slots than templates: make the regex distinct
             rx, w = rx + " r%d" % k, w + " r%d" % k
         lib["patterns"][i]["primary_pattern"]["regex"] = rx
         lib["patterns"][i]["name"] = "short: " + rx

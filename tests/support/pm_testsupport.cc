@@ -134,8 +134,11 @@ int pmt_filter_triggers(pmt_lib *l, int p, const uint8_t *text, size_t n, int ph
     const uint32_t *gc = (const uint32_t *)(b + h->off_gram_count);
     const Probe *pr = (const Probe *)(b + h->off_probes);
     const uint8_t *lp = b + h->off_litpool;
-    size_t first = (4 - (size_t)phase) & 3;
-    for (size_t i = first; i + 4 <= n; i += 4) {
+    // the kernel tests the word at every text offset that is a multiple of the filter's granule (4, or 2 for libraries
+    // with 5-byte literals); `phase` is the offset of text[0] in that grid
+    const size_t gran = h->filter_granule == 2 ? 2 : 4;
+    size_t first = (gran - (size_t)phase % gran) % gran;
+    for (size_t i = first; i + 4 <= n; i += gran) {
         uint32_t g;
         memcpy(&g, text + i, 4);
         if (h->filter_fold) g |= 0x20202020u;

@@ -104,6 +104,33 @@ def test_alignment_sweep(engine):
     check_parity(engine, lib_json, logs, expect_events=120)
 
 
+def test_short_literals_stay_on_the_filter(engine):
+    """Required literals of 5 and 6 bytes (FATAL, panic:, Killed, (?i)error ...): the library compiles to filter
+    granule 2 (k_scan_half tests the word at every even offset) instead of sending these patterns through the combined
+    DFA.  A literal must be found at every alignment, across 16-byte, 512-byte and 2 KiB boundaries and at pod ends."""
+    regs = [r"FATAL: \d+", r"panic: ", r"Killed process \d+", r"(?i)error \d+", r"status=5\d\d", r"OutOfMemoryError", r"\bEPIPE\b", r"[Cc]ache (evicted|flushed)"]
+    lib_json = lib_of(regs, context_extraction={"lines_before": 2, "lines_after": 2})
+    rep = engine.compile_library(lib_json).publish().report
+    assert rep["n_dfa_scanned"] == 0 and rep["n_filtered"] == len(regs)
+    logs = []
+    for k in range(0, 70):
+        logs.append(("a" * k + "FATAL: 12 " + "b" * (k % 7) + "\n" + "c" * k + " go panic: nil map\n" + "x" * (2040 - k) + "Killed process 77 at the tile edge").encode())
+        logs.append(("d" * (500 + k) + "eRRoR 404 " + "e" * k + " status=503\n" + "f" * k + "EPIPE\n" + "g" * (k % 3) + "Cache evicted\nxEPIPEx FATAL:\n").encode())
+        logs.append(("h" * k + "java.lang.OutOfMemoryError").encode())
+    check_parity(engine, lib_json, logs, expect_events=450)
+    # and on generated text with these patterns mixed into a synthetic library (still no DFA pass)
+    lib2, wit, swit = synth.make_library(60)
+    for i, rx in enumerate(regs):
+        lib2["patterns"][i * 7]["primary_pattern"]["regex"] = rx
+    wit2 = list(wit)
+    for i, w in enumerate(["FATAL: 7", "panic: x", "Killed process 1", "ERROR 9", "status=500", "OutOfMemoryError", "EPIPE", "cache flushed"]):
+        wit2[i * 7] = w
+    rep = engine.compile_library(lib2).publish().report
+    assert rep["n_dfa_scanned"] == 0
+    corpus, _ = synth.make_corpus(3 << 20, wit2, swit, p_hit=5e-3)
+    check_parity(engine, lib2, [corpus], expect_events=80)
+
+
 def test_secondary_scoring_and_windows(engine):
     T = chr(9)
     lib_json = {"patterns": [
