@@ -2110,13 +2110,16 @@ cudaError_t launch_export(EventOut src, EventOut dst_host, const unsigned long l
 }
 
 cudaError_t launch_sort_small(const unsigned long long *raw, ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
-                              unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s) {
+                              unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, int num_sms, cudaStream_t s) {
     unsigned long long *buf_a = scratch, *buf_b = scratch + kMediumSort;
     k_sort_chunks<<<kSortChunksMedium, kSortChunk / 2, 0, s>>>(raw, ctr, raw_cap, buf_a);
     cudaError_t e = cudaFuncSetAttribute(k_sort_merge, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSort * 8);
     if (e != cudaSuccess) return e;
     k_sort_merge<<<kSortChunksSmall, 1024, kSmallSort * 8, s>>>(buf_a, ctr, raw_cap, buf_b);           // n <= kSmallSort, else returns at once
-    k_merge_all<<<kMergeCtas, kMergeThreads, 0, s>>>(buf_a, buf_b, ctr, raw_cap);                       // n >  kSmallSort, else returns at once
+    // every CTA of this grid waits for all the others at a barrier: never more CTAs than the SMs it may run on can hold at
+    // once (a green-context partition can be as small as 8 SMs)
+    const int merge_ctas = std::max(1, std::min(kMergeCtas, num_sms * 4));
+    k_merge_all<<<merge_ctas, kMergeThreads, 0, s>>>(buf_a, buf_b, ctr, raw_cap);                       // n >  kSmallSort, else returns at once
     k_sort_unique<<<1, 1024, 0, s>>>(buf_b, ctr, raw_cap, uniq, n_unique, big_flag);                   // an odd number of passes: the result is in b
     k_rank<<<64, 256, 0, s>>>(raw, ctr, raw_cap, uniq, n_unique, reinterpret_cast<uint32_t *>(buf_a));   // a is free again
     return cudaGetLastError();

@@ -138,7 +138,7 @@ constexpr int kSmallSort = 16384, kMediumSort = 131072;
 // Five launches (those of the path that does not apply return at once); `scratch` holds 2 * kMediumSort u64.  Afterwards the
 // first kMediumSort u32 of `scratch` hold, for every raw key, its rank in uniq (what k_finalize needs to place the key's row).
 cudaError_t launch_sort_small(const unsigned long long *raw, ScanCounters *ctr, unsigned long long raw_cap, unsigned long long *scratch,
-                              unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, cudaStream_t s);
+                              unsigned long long *uniq, unsigned long long *n_unique, unsigned int *big_flag, int num_sms, cudaStream_t s);
 // Gram profile: counts, for every aligned word of text[0, sample_bytes), the occurrences of the
 // keys of an open-addressing table (keys: 2^log2_cap u32, kGramEmpty = free; counts zeroed by the
 // caller).  Used once per library to learn which literal grams are frequent in the real logs.

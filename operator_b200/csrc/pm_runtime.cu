@@ -871,7 +871,7 @@ int scan_async(pm_batch *b) {
         CU(launch_sort_small(w.raw.as<unsigned long long>(), w.ctr.as<ScanCounters>(), w.raw_cap, w.sort_scratch.as<unsigned long long>(),
                              w.uniq.as<unsigned long long>(),
                              reinterpret_cast<unsigned long long *>(w.ctr.as<char>() + kOffUnique),
-                             reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.stream3));
+                             reinterpret_cast<unsigned int *>(w.ctr.as<char>() + kOffBig), w.sms_post, w.stream3));
         CU(cudaEventRecord(w.join_ev[2], w.stream3));
         w.launches += 5;
         CU(cudaStreamWaitEvent(w.stream, w.join_ev[0], 0));
@@ -1424,6 +1424,14 @@ int pm_batch_add_pod_device(pm_batch *b, const void *d_log, size_t n, uint64_t t
     }
     // Java's split drops trailing "\r?\n" separators: look at the end of the log, 4 KiB at a time.  A byte is kept
     // when it is neither '\r' nor '\n', or a '\r' that is not followed by '\n'; the effective end is behind the last kept byte.
+    int previous = -1;
+    cudaGetDevice(&previous);
+    struct Restore {   // leave the caller's current device as it was
+        int dev;
+        ~Restore() {
+            if (dev >= 0) cudaSetDevice(dev);
+        }
+    } restore{previous};
     CU(cudaSetDevice(ordinal));
     std::vector<uint8_t> tail(4097);
     size_t eff = 0, hi = n;

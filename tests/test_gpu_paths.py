@@ -44,6 +44,7 @@ def test_overflow_rerun_paths(tmp_path):
     assert r.returncode == 0 and "tiny-queues ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
 
 
+@pytest.mark.timeout(300)
 def test_many_raw_events_take_the_merge_passes(engine):
     """More than 16384 raw events: the shared-memory rank merge declines, the seven merge rounds of k_merge_all order
     them on the device (up to 131072).  Every field against the oracle."""
@@ -51,6 +52,14 @@ def test_many_raw_events_take_the_merge_passes(engine):
     corpus, n_lines = synth.make_corpus(12 << 20, wit, swit, p_hit=0.25)
     res = check_parity(engine, lib_json, [corpus], expect_events=17000)
     assert res.n_events > 16384
+    # the merge rounds wait for each other at a grid-wide barrier: with the post-scan kernels confined to a small
+    # green-context partition (8 SMs) the grid must still fit it at once
+    engine.set_pipeline(2, 8)
+    try:
+        res2 = check_parity(engine, lib_json, [corpus], expect_events=17000)
+        assert res2.n_events == res.n_events
+    finally:
+        engine.set_pipeline(1, 0)
 
 
 @pytest.mark.skipif(not pcre2_oracle.available(), reason="libpcre2-8 not loadable")
