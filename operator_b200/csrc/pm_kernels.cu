@@ -1514,12 +1514,14 @@ __device__ void warp_collect_backward(const uint8_t *text, unsigned long long be
     __syncwarp();
 }
 
+// (StackFirst: pm_kernels.h - the bytes a STACK line can start with)
 __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
                                                           const unsigned long long *__restrict__ tile_prefix, PodTable pt,
                                                           const unsigned long long *__restrict__ keys, const unsigned long long *n_keys_ptr,
                                                           unsigned long long key_cap,
                                                           Item *__restrict__ items, unsigned long long item_cap, uint32_t *__restrict__ long_list,
-                                                          unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr, int slots) {
+                                                          unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr, int slots,
+                                                          const StackFirst stack_first) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned long long *fwd = reinterpret_cast<unsigned long long *>(smem_raw) + (size_t)warp * 2 * slots;   // fwd[i]: '\n' that ends line L+i
@@ -1550,10 +1552,9 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
         const long long n_lines = pod.n_lines;
         const int nb = (int)min((long long)pd.lines_before, L - 1);
         const int na = (int)min((long long)pd.lines_after, n_lines - L);
-        const int stack_cap = pd.include_stack ? (int)min((long long)kStackMax, n_lines - L) : 0;
-        const int n_stack = max(0, stack_cap - na);
-        int need_f = max(na, stack_cap), need_b = nb;
-        unsigned long long n_items = (unsigned long long)n_stack;
+        int stack_cap = pd.include_stack ? (int)min((long long)kStackMax, n_lines - L) : 0;
+        int need_f = na, need_b = nb;
+        unsigned long long n_items = 0;
         for (uint32_t j = 0; j < pd.sec_count; j++) {
             int w = sds[pd.sec_first + j].window;
             need_f = max(need_f, (int)min((long long)w, n_lines - L));
@@ -1561,6 +1562,24 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
             n_items += 2ull * w + 1;
         }
         warp_collect_forward(text, ls, need_f + 1, fwd);
+        if (stack_cap > need_f) {
+            // The STACK extension (SPEC.md section 6) wants up to 50 more lines, ~7 KB of text per event - but only while
+            // they are stack-trace lines.  Its regex is anchored at the line start, so the first byte of the first candidate
+            // line decides whether the run can start at all: most hit lines are not followed by a frame, and then neither
+            // the lines are collected nor the 50 work items created (half of k_plan's instructions and of k_check's items).
+            __syncwarp();
+            const unsigned long long q = fwd[na] + 1;   // start of line L + na + 1 (it exists: stack_cap > na)
+            const uint32_t b0 = text[q];
+            if ((stack_first.bits[b0 >> 5] >> (b0 & 31u)) & 1u) {
+                need_f = stack_cap;
+                __syncwarp();
+                warp_collect_forward(text, ls, need_f + 1, fwd);
+            } else {
+                stack_cap = 0;
+            }
+        }
+        const int n_stack = max(0, stack_cap - na);
+        n_items += (unsigned long long)n_stack;
         if (lane == 0) bwd[0] = ls - 1;
         if (need_b > 0) warp_collect_backward(text, ls - 1, need_b, bwd + 1);
         __syncwarp();
@@ -2045,7 +2064,7 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
         if (e != cudaSuccess) return e;
     }
     k_plan<<<blocks, kPlanWarps * 32, plan_smem, s>>>(text, lib.blob, lib.h, tile_prefix, pt, keys, n_keys_dev, key_cap, items, rs.item_cap,
-                                                      rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots);
+                                                      rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots, lib.stack_first);
     stage_mark("k_plan");
     // short and long lines are independent: walk them concurrently when a side stream is given.  (Both in one
     // launch, the long lines on warp_walk_line in the first CTAs of the grid, was measured in round 2: 47 us

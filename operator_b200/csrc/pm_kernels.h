@@ -41,10 +41,17 @@ struct FilterView {
     uint32_t granule = 4;   // 4: k_scan tests the aligned words; 2: every even offset (pm_blob.h)
 };
 
+// The bytes a line matching the built-in STACK regex can start with (bit b of the 256-bit set), derived from the unit's
+// DFA at publish time: k_plan looks at one byte before it collects the lines of a possible stack trace.
+struct StackFirst {
+    uint32_t bits[8];
+};
+
 struct DeviceLibrary {
     const uint8_t *blob = nullptr;      // device copy of the compiled blob
     FilterView fv;
     int ctx_slots = 0;                  // newline slots k_plan needs per direction (largest window of the library + 2)
+    StackFirst stack_first = {{0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}};
     uint32_t verify_table_cap = 0;      // bytes of shared memory k_verify gives each warp for its task's table (0: walk through L1)
     BlobHeader h;                       // host copy of the blob header
 };

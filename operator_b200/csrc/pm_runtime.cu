@@ -1328,6 +1328,23 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
                 }
                 for (uint32_t i = 0; i < bh.n_secondaries; i++) need = std::max(need, sdv[i].window);
                 l->dev[d].ctx_slots = need + 2;
+                {   // first bytes of STACK lines: from the start state, every byte that does not lead to the dead state
+                    const UnitDesc &su = reinterpret_cast<const UnitDesc *>(hb + bh.off_units)[bh.stack_unit];
+                    const uint16_t *tab = reinterpret_cast<const uint16_t *>(hb + bh.off_tables) + su.table_off;
+                    const uint8_t *cm = hb + bh.off_classmaps + su.classmap_off;
+                    StackFirst sf;
+                    memset(&sf, 0, sizeof sf);
+                    for (int b = 0; b < 256; b++) {
+                        const bool alive = su.dead_state == 0xFFFF || tab[cm[b]] != su.dead_state;
+                        if (alive) sf.bits[b >> 5] |= 1u << (b & 31);
+                    }
+                    // an empty line presents its '\n' (or the '\r' of "\r\n") as first byte: allowed only if the unit accepts the empty line
+                    const bool empty_ok = tab[su.stride - 1] == su.accept_state;
+                    sf.bits['\n' >> 5] &= ~(1u << ('\n' & 31));
+                    if (empty_ok) sf.bits['\n' >> 5] |= 1u << ('\n' & 31);
+                    sf.bits['\r' >> 5] |= 1u << ('\r' & 31);   // could be the separator's '\r' or text: let the full path decide
+                    l->dev[d].stack_first = sf;
+                }
                 // k_verify copies a task's table into shared memory when it fits the per-warp budget: the largest
                 // table among the filtered primaries, capped so that 4 warps x budget + 3 KiB still lets 11-12 CTAs share an SM
                 const UnitDesc *udv = reinterpret_cast<const UnitDesc *>(hb + bh.off_units);
