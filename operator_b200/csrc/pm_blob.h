@@ -24,7 +24,7 @@
 namespace pm {
 
 constexpr uint32_t kBlobMagic = 0x424C4D50u;   // "PMLB"
-constexpr uint32_t kBlobVersion = 9;
+constexpr uint32_t kBlobVersion = 10;
 constexpr int kGramLen = 4;        // bytes per gram = one aligned 32-bit text word
 constexpr int kMinLiteral = 7;     // any 7-byte window covers one aligned 4-byte word
 // Granule of the gram filter: the text offsets whose 4-byte word k_scan tests are the multiples of it.
@@ -66,7 +66,7 @@ struct UnitDesc {
     uint16_t nstates, stride, accept_state;
     uint16_t mid_state;      // state after one byte that belongs to no pattern (speculative walk entry guess)
     uint16_t dead_state;     // state from which acceptance is unreachable, 0xFFFF if none (anchored regexes)
-    uint16_t pad;
+    uint16_t literal_is_match;   // 1: the pattern's required literals are all it can match (pm_literal.h): k_verify skips the walk
     uint32_t wide_off;       // u16 elements from off_tables: 256-column copy (index = state*256 + byte) for the
                              // units the resolve stage walks most (STACK, secondaries); 0xFFFFFFFF if absent
 };

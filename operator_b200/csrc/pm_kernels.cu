@@ -842,7 +842,11 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
         const uint32_t tbytes = (uint32_t)ud.nstates * ud.stride * 2u;
         const bool staged = tbytes <= table_cap;   // warp-uniform
         unsigned char *stab = s_tables + (size_t)warp * table_cap;
-        if (staged) {   // tables start 16-byte aligned in the blob and are followed by at least their padding
+        // a pattern that is nothing but its literal(s): k_confirm's comparison was the match, only the line start is
+        // still needed (warp-uniform)
+        const bool lit = ud.literal_is_match != 0;
+        if (lit) {
+        } else if (staged) {   // tables start 16-byte aligned in the blob and are followed by at least their padding
             __syncwarp();
             for (uint32_t off = lane * 16u; off < tbytes; off += 512u)
                 *reinterpret_cast<uint4 *>(stab + off) = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(gtab) + off));
@@ -858,6 +862,8 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
             int src = 16 + __ffs(fwd) - 1;
             uint32_t mm = __shfl_sync(FULL, m, src);
             le = p16 + 16ull * (src - 16) + (__ffs(mm) - 1);
+        } else if (lit) {
+            le = p;   // not needed
         } else {   // a long line: keep looking, 512 bytes per round trip (the text is '\n'-padded up to `total`)
             le = total;
             for (unsigned long long q = p16 + 256; q < total; q += 512) {
@@ -891,9 +897,20 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
                 }
             }
         }
+        const uint32_t stride = ud.stride, acc = ud.accept_state;
+        if (lit) {
+            if (lane == 0) {
+                unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
+                if (at < raw_cap)
+                    raw[at] = (ls << kPatternBits) | pat;
+                else
+                    ctr->raw_overflow = 1;
+            }
+            __syncwarp();
+            continue;
+        }
         const unsigned long long lend = strip_cr(text, pt, ls, le);
         // ---- the walk (class map and first piece of the line travel together)
-        const uint32_t stride = ud.stride, acc = ud.accept_state;
         uint32_t st = staged ? warp_walk_line<true>(text, ls, lend, reinterpret_cast<const uint16_t *>(stab), stride, acc, ud.dead_state, ud.mid_state,
                                                     blob + h.off_classmaps + ud.classmap_off, s_cmap[warp], s_cls[warp])
                              : warp_walk_line<false>(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, blob + h.off_classmaps + ud.classmap_off,

@@ -428,10 +428,14 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
         const int granule = (allow_half && shortest >= kMinLiteralHalf && shortest < kMinLiteral) ? 2 : 4;
         const int min_literal = granule == 2 ? kMinLiteralHalf : kMinLiteral;
         out.granule = granule;
+        std::vector<char> unit_literal_is_match(units.size(), 0);
+        static const bool allow_literal_match = getenv("PM_NO_LITERAL_MATCH") == nullptr;
         for (int i = 0; i < P; i++) {
             if (quality_of[i] >= min_literal) {
                 out.literals[i] = std::move(lits_of[i]);
                 pdesc[i].tier = 1;
+                // a plain literal (or an alternation of them): finding it IS the match, k_verify has nothing to walk
+                if (allow_literal_match && literal_hit_is_match(*asts[i], out.literals[i])) unit_literal_is_match[pdesc[i].unit] = 1;
             } else {
                 pdesc[i].tier = 2;
                 tier2.push_back(i);
@@ -483,6 +487,7 @@ int compile_library(const char *spec, size_t n, CompiledLibrary &out, pm_compile
             }
             u.nstates = (uint16_t)d.nstates;
             u.stride = (uint16_t)d.stride();
+            u.literal_is_match = unit_literal_is_match[ui];
             u.accept_state = (uint16_t)d.first_accept;   // early-accept: one sticky state
             // mid-line idle state: where the DFA sits after one byte that belongs to no pattern;
             // the entry-state guess of the speculative long-line walk (k_check_long)

@@ -194,6 +194,38 @@ Info analyse(const Node &n) {
 
 }  // namespace
 
+namespace {
+
+// Only nodes whose match is a fixed byte string chosen from a finite set, with nothing asserted about
+// the text around it (no anchors, no word boundaries: analyse() counts those as "the empty string").
+bool plain_strings_only(const Node &n) {
+    switch (n.kind) {
+        case NodeKind::Lit: return n.cp < 0x80 && n.cp != '\n' && n.cp != '\r';
+        case NodeKind::Set:
+            for (auto &x : n.ranges)
+                if (x.second >= 0x80 || (x.first <= '\n' && '\n' <= x.second) || (x.first <= '\r' && '\r' <= x.second)) return false;
+            return true;
+        case NodeKind::Empty: return true;
+        case NodeKind::Cat: case NodeKind::Alt: case NodeKind::Rep:
+            for (auto &k : n.kids)
+                if (!plain_strings_only(*k)) return false;
+            return true;
+        default: return false;
+    }
+}
+
+}  // namespace
+
+bool literal_hit_is_match(const Node &ast, const std::vector<Literal> &chosen) {
+    if (chosen.empty() || !plain_strings_only(ast)) return false;
+    Info i = analyse(ast);
+    if (!i.has_exact) return false;
+    std::vector<Literal> ex = i.exact, ch = chosen;
+    dedup(ex);
+    dedup(ch);
+    return ex == ch;
+}
+
 std::vector<Literal> required_literals(const Node &ast, int *min_len) {
     Info i = analyse(ast);
     std::vector<Literal> best = i.req;

@@ -23,6 +23,12 @@ struct Literal {
 // returned in *min_len.
 std::vector<Literal> required_literals(const Node &ast, int *min_len);
 
+// True when `chosen` (the set required_literals returned for `ast`) is EVERY string the regex can match and
+// the regex asserts nothing about the text around the match: an ASCII literal, an alternation of literals,
+// "(?i)..." over such.  An occurrence of any member in a line is then a match of the line (Matcher.find()),
+// and the confirm stage's literal comparison needs no DFA walk behind it (UnitDesc::literal_is_match).
+bool literal_hit_is_match(const Node &ast, const std::vector<Literal> &chosen);
+
 // Estimated commonness of a byte in log text (static table), -log2 probability scaled.
 int byte_rarity(uint8_t b);
 

@@ -77,6 +77,11 @@ int pmt_secondary_match(pmt_lib *l, int p, int j, const uint8_t *line, size_t n)
 int pmt_stack_match(pmt_lib *l, const uint8_t *line, size_t n) {
     return dfa_line_accepts(l->lib.unit_dfas[l->lib.header()->stack_unit], line, n, nullptr);
 }
+// 1 when k_verify treats a confirmed literal of pattern p as the match itself (UnitDesc::literal_is_match)
+int pmt_literal_is_match(pmt_lib *l, int p) {
+    const UnitDesc *ud = reinterpret_cast<const UnitDesc *>(l->lib.blob.data() + l->lib.header()->off_units);
+    return ud[pdesc(l)[p].unit].literal_is_match;
+}
 int pmt_unit_states(pmt_lib *l, int p) { return l->lib.unit_dfas[pdesc(l)[p].unit].nstates; }
 
 // Combined DFAs: which tier-2 patterns does the line match?  Returns the count written.

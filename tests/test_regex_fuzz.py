@@ -102,3 +102,102 @@ def test_three_engines_agree_on_random_regexes(harness):
     print('fuzz: %d pairs, %d matches, %d rejected regexes' % (n_pairs, n_match, n_rejected))
     assert n_pairs > 100000 and n_match > 2000, (n_pairs, n_match)
     assert n_rejected < N_BATCHES * REGEXES_PER_BATCH // 3, n_rejected
+
+
+# ---- patterns that are nothing but their literals: k_verify takes the confirmed literal as the match
+# (UnitDesc::literal_is_match, pm_literal.cc literal_hit_is_match).  Sound iff "a member of the literal set
+# occurs in the line" and "the regex finds a match in the line" are the same predicate.
+
+_PLAIN_FLAGGED = [
+    r"OutOfMemoryError", r"(?i)connection refused", r"(timeout exceeded|deadline exceeded)", r"Fail(ed|ure) to bind",
+    r"exit code 13[79] seen", r"\QTypeError: x.y(z)\E", r"segfault at 0x0{4}", r"killed by signal 9!?",
+]
+_PLAIN_NOT_FLAGGED = [
+    r"\bfatal error\b", r"^ERROR happened", r"failed to start$", r"error: .*failed", r"exit code [0-9]+ seen",
+    "naïve résumé x", r"retrying \w+ connection", r"disk full\r",
+]
+
+
+def test_literal_is_match_flag_known_cases(harness):
+    harness.L.pmt_literal_is_match.argtypes = [__import__("ctypes").c_void_p, __import__("ctypes").c_int]
+    rc, h, rep = harness.compile_regexes(_PLAIN_FLAGGED + _PLAIN_NOT_FLAGGED)
+    assert rc == 0, rep.message
+    flags = [harness.L.pmt_literal_is_match(h, i) for i in range(len(_PLAIN_FLAGGED) + len(_PLAIN_NOT_FLAGGED))]
+    harness.L.pmt_free(h)
+    assert flags[:len(_PLAIN_FLAGGED)] == [1] * len(_PLAIN_FLAGGED), list(zip(_PLAIN_FLAGGED, flags))
+    assert flags[len(_PLAIN_FLAGGED):] == [0] * len(_PLAIN_NOT_FLAGGED), list(zip(_PLAIN_NOT_FLAGGED, flags[len(_PLAIN_FLAGGED):]))
+
+
+def _plain_regex(rnd):
+    """(regex, sample strings): a literal, an alternation, small sets and optional pieces, maybe (?i)."""
+    alphabet = "abcdeXYZ 019:_-./"
+    def word(lo, hi):
+        return "".join(rnd.choice(alphabet) for _ in range(rnd.randint(lo, hi)))
+    def esc(s):
+        return "".join("\\" + c if c in ".-/" and rnd.random() < 0.7 else c for c in s)
+    kind = rnd.randrange(5)
+    if kind == 0:
+        w = word(7, 18)
+        rx, samples = esc(w), [w]
+    elif kind == 1:
+        ws = [word(7, 14) for _ in range(rnd.randint(2, 4))]
+        rx, samples = "(" + "|".join(esc(w) for w in ws) + ")", ws
+    elif kind == 2:
+        a, b, c = word(4, 8), word(1, 3), word(4, 8)
+        rx, samples = "%s(%s)?%s" % (esc(a), esc(b), esc(c)), [a + c, a + b + c]
+    elif kind == 3:
+        a, c = word(4, 8), word(4, 8)
+        rx, samples = "%s[ab]%s" % (esc(a), esc(c)), [a + "a" + c, a + "b" + c]
+    else:
+        a, c = word(3, 6), word(4, 8)
+        rx, samples = "%s(XY|01){2}%s" % (esc(a), esc(c)), [a + "XY01" + c, a + "0101" + c]
+    if rnd.random() < 0.4:
+        rx = "(?i)" + rx
+        samples = samples + [s.upper() for s in samples] + [s.swapcase() for s in samples]
+    return rx, samples
+
+
+def test_literal_is_match_is_the_regex(harness):
+    import ctypes
+    import re
+    harness.L.pmt_literal_is_match.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    rnd = random.Random(SEED + 1)
+    alphabet = "abcdeXYZ 019:_-./"
+    n_flagged = n_pairs = n_hits = 0
+    for _ in range(6):
+        regexes, samples = [], []
+        while len(regexes) < 40:
+            rx, sm = _plain_regex(rnd)
+            try:
+                javaregex.parse(rx)
+            except javaregex.JavaRegexError:
+                continue
+            regexes.append(rx)
+            samples.append(sm)
+        rc, h, rep = harness.compile_regexes(regexes)
+        assert rc == 0, rep.message
+        lines = []
+        for sm in samples:
+            for s in sm[:4]:
+                pre = "".join(rnd.choice(alphabet) for _ in range(rnd.randint(0, 9)))
+                lines.append(pre + s + " tail")
+                k = rnd.randrange(len(s))
+                lines.append(pre + s[:k] + ("#" if s[k] != "#" else "%") + s[k + 1:])    # one byte off
+                lines.append(pre + s[:-1])                                               # cut short
+                lines.append(pre + s.swapcase() + ".")                                    # case flipped
+        pys = [re.compile(javaregex.to_python(rx), re.ASCII) for rx in regexes]
+        for pi, rx in enumerate(regexes):
+            if not harness.L.pmt_literal_is_match(h, pi):
+                continue
+            n_flagged += 1
+            for line in lines:
+                raw = line.encode()
+                want = pys[pi].search(line) is not None
+                n_pairs += 1
+                n_hits += want
+                for phase in range(4):
+                    got = bool(harness.L.pmt_filter_triggers(h, pi, raw, len(raw), phase))
+                    assert got == want, (rx, line, phase, got, want)
+        harness.L.pmt_free(h)
+    print("literal-is-match: %d flagged patterns, %d pairs, %d hits" % (n_flagged, n_pairs, n_hits))
+    assert n_flagged > 150 and n_hits > 500, (n_flagged, n_hits)
