@@ -1350,7 +1350,7 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
                 const UnitDesc *udv = reinterpret_cast<const UnitDesc *>(hb + bh.off_units);
                 uint32_t cap = 0;
                 for (uint32_t i = 0; i < bh.n_patterns; i++)
-                    if (pdv[i].tier == 1) cap = std::max(cap, (uint32_t)udv[pdv[i].unit].nstates * udv[pdv[i].unit].stride * 2u);
+                    if (pdv[i].tier == 1 && !udv[pdv[i].unit].literal_is_match) cap = std::max(cap, (uint32_t)udv[pdv[i].unit].nstates * udv[pdv[i].unit].stride * 2u);
                 static const uint32_t cap_max = getenv("PM_VERIFY_TABLE_CAP") ? (uint32_t)atoi(getenv("PM_VERIFY_TABLE_CAP")) : 4096u;
                 l->dev[d].verify_table_cap = std::min((cap + 255u) & ~255u, cap_max);
             }
