@@ -72,6 +72,28 @@ __device__ __forceinline__ unsigned lanemask_lt() {
     return m;
 }
 
+// ---- warp time stamps (-DPM_TRACE builds only; tools_warp_trace.py): where the time of the small post-scan
+// kernels goes.  Region r holds 8 stamps for each of the first kTraceWarps warps of one kernel.
+#ifdef PM_TRACE
+constexpr unsigned kTraceWarps = 16384, kTraceRegions = 4;
+__device__ unsigned long long g_trace[kTraceRegions * kTraceWarps * 8];
+__device__ __forceinline__ void trace_stamp(unsigned region, unsigned long long warp, unsigned slot) {
+    if ((threadIdx.x & 31) == 0 && warp < kTraceWarps) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_trace[((unsigned long long)region * kTraceWarps + warp) * 8 + slot] = t;
+    }
+}
+__device__ __forceinline__ void trace_value(unsigned region, unsigned long long warp, unsigned slot, unsigned long long v) {
+    if ((threadIdx.x & 31) == 0 && warp < kTraceWarps) g_trace[((unsigned long long)region * kTraceWarps + warp) * 8 + slot] = v;
+}
+#define PM_TR(region, warp, slot) trace_stamp(region, warp, slot)
+#define PM_TV(region, warp, slot, v) trace_value(region, warp, slot, v)
+#else
+#define PM_TR(region, warp, slot) ((void)0)
+#define PM_TV(region, warp, slot, v) ((void)0)
+#endif
+
 // ------------------------------------------------------------------------------------ confirm
 // What a warp needs to turn one filter hit into verify tasks.
 struct ConfirmParams {
@@ -604,22 +626,26 @@ __device__ __forceinline__ UnitTables unit_tables(const uint8_t *blob, const Blo
 __device__ bool line_matches(const uint8_t *text, unsigned long long a, unsigned long long b, const UnitTables &t) {
     uint32_t s = 0;
     if (t.wide) {
-        // 256-column table: one dependent lookup per byte; text read as aligned 32-bit words.  The
-        // accepting state is sticky and the dead state absorbing, so both are tested once per word.
+        // 256-column table: one dependent lookup per byte.  The text comes in aligned 16-byte pieces: the lanes of a warp
+        // walk 32 different lines, so every text load of the warp touches 32 cache lines, and with 4-byte loads those
+        // were 60 % of the L1 wavefronts this kernel is bound by (tools_warp_trace.py: 110 ns per line byte).  The
+        // accepting state is sticky and the dead state absorbing, so both are tested once per piece.
         const uint16_t *w = t.wide;
-        unsigned long long p = a;
-        for (; p < b && (p & 3); p++) s = w[(s << 8) | text[p]];
-        for (; p + 4 <= b && s != t.accept && s != t.dead; p += 4) {
-            const uint32_t x = *reinterpret_cast<const uint32_t *>(text + p);
-            s = w[(s << 8) | (x & 0xFFu)];
-            s = w[(s << 8) | ((x >> 8) & 0xFFu)];
-            s = w[(s << 8) | ((x >> 16) & 0xFFu)];
-            s = w[(s << 8) | (x >> 24)];
+        for (unsigned long long p = a & ~15ull; p < b && s != t.accept && s != t.dead; p += 16) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(text + p);
+            const uint32_t x[4] = {v.x, v.y, v.z, v.w};
+            if (p >= a && p + 16 <= b) {
+#pragma unroll
+                for (int j = 0; j < 16; j++) s = w[(s << 8) | ((x[j >> 2] >> (8 * (j & 3))) & 0xFFu)];
+            } else {   // first / last piece of the line
+                const int lo = p >= a ? 0 : (int)(a - p), hi = p + 16 <= b ? 16 : (int)(b - p);
+#pragma unroll
+                for (int j = 0; j < 16; j++)
+                    if (j >= lo && j < hi) s = w[(s << 8) | ((x[j >> 2] >> (8 * (j & 3))) & 0xFFu)];
+            }
         }
         if (s == t.accept) return true;
         if (s == t.dead) return false;
-        for (; p < b; p++) s = w[(s << 8) | text[p]];
-        if (s == t.accept) return true;
         s = t.tab[s * t.stride + t.stride - 1];
         return s == t.accept;
     }
@@ -685,13 +711,16 @@ __global__ void __launch_bounds__(256) k_confirm(const uint8_t *__restrict__ tex
     cp.text = text, cp.total = total, cp.gkeys = fv.gkeys, cp.gfirst = fv.gfirst, cp.gcount = fv.gcount, cp.probes = fv.probes, cp.litpool = fv.litpool;
     cp.log2_cap = fv.log2_cap, cp.fold = fv.fold, cp.tasks = tasks, cp.task_cap = task_cap;
     const bool half = fv.granule == 2;   // (group << 8) | 8 even offsets, else (group << 4) | 4 aligned words
+    PM_TR(0, ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, 0);
     for (unsigned long long i = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += n_warps) {
         const unsigned long long e = cand[i];
+        PM_TR(0, ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, 1);
         if (half)
             confirm_candidate(cp, ctr, e >> 8, (uint32_t)(e & 255u), 2u);
         else
             confirm_candidate(cp, ctr, e >> 4, (uint32_t)(e & 15u), 4u);
     }
+    PM_TR(0, ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, 2);
 }
 
 // One warp walks one line [a, b) through a unit DFA and returns the state after the last byte
@@ -825,9 +854,11 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
     const unsigned long long n = ctr->n_verified < task_cap ? ctr->n_verified : task_cap;
     const PatternDesc *pd = reinterpret_cast<const PatternDesc *>(blob + h.off_patterns);
     const unsigned long long n_warps = (unsigned long long)gridDim.x * kVerifyWarps;
+    PM_TR(1, (unsigned long long)blockIdx.x * kVerifyWarps + warp, 0);
     for (unsigned long long i = (unsigned long long)blockIdx.x * kVerifyWarps + warp; i < n; i += n_warps) {
         const unsigned long long t = tasks[i], p = t >> kPatternBits;
         const uint32_t pat = (uint32_t)(t & ((1u << kPatternBits) - 1u));
+        PM_TR(1, i, 1);
         // ---- line bounds: 16 lanes look back, 16 lanes look ahead, 256 bytes each, one round trip;
         //      the pattern's descriptors are fetched under it, and the table's lines after them
         const unsigned long long p16 = p & ~15ull;
@@ -854,6 +885,7 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
             warp_touch_table(gtab, tbytes);
         }
         uint32_t m = newline_mask16(around);
+        PM_TR(1, i, 2);
         if (lane == 16) m &= ~((1u << (p - p16)) - 1u);          // forward search starts at p
         unsigned has = __ballot_sync(FULL, m != 0);
         unsigned long long ls, le;
@@ -898,7 +930,9 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
             }
         }
         const uint32_t stride = ud.stride, acc = ud.accept_state;
+        PM_TR(1, i, 3);
         if (lit) {
+            PM_TR(1, i, 5);
             if (lane == 0) {
                 unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
                 if (at < raw_cap)
@@ -916,6 +950,9 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
                              : warp_walk_line<false>(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, blob + h.off_classmaps + ud.classmap_off,
                                                      s_cmap[warp], s_cls[warp]);
         if (st != acc) st = __ldg(gtab + (st * stride + stride - 1));
+        PM_TR(1, i, 4);
+        PM_TV(1, i, 6, lend - ls);
+        PM_TV(1, i, 7, ((unsigned long long)tbytes << 1) | (staged ? 1u : 0u));
         if (lane == 0) {
             if (st == acc) {
                 unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);
@@ -1555,7 +1592,9 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
         return;
     }
 
+    PM_TR(2, (unsigned long long)blockIdx.x * kPlanWarps + warp, 0);
     for (unsigned long long ev = (unsigned long long)blockIdx.x * kPlanWarps + warp; ev < n_events; ev += (unsigned long long)gridDim.x * kPlanWarps) {
+        PM_TR(2, ev, 1);
         const unsigned long long key = keys[ev], ls = key >> kPatternBits;
         const uint32_t pat = (uint32_t)(key & ((1u << kPatternBits) - 1u));
         const PatternDesc pd = pds[pat];
@@ -1565,7 +1604,9 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
             if (pods[mid].start <= ls) lo = mid; else hi = mid - 1;
         }
         const PodDev pod = pods[lo];
+        PM_TR(2, ev, 2);
         const long long L = (long long)(warp_newlines_before(text, tile_prefix, ls) - pod.nl_before) + 1;
+        PM_TR(2, ev, 3);
         const long long n_lines = pod.n_lines;
         const int nb = (int)min((long long)pd.lines_before, L - 1);
         const int na = (int)min((long long)pd.lines_after, n_lines - L);
@@ -1597,9 +1638,11 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
         }
         const int n_stack = max(0, stack_cap - na);
         n_items += (unsigned long long)n_stack;
+        PM_TR(2, ev, 4);
         if (lane == 0) bwd[0] = ls - 1;
         if (need_b > 0) warp_collect_backward(text, ls - 1, need_b, bwd + 1);
         __syncwarp();
+        PM_TR(2, ev, 5);
 
         auto line_span = [&](int rel, unsigned long long &a, unsigned long long &b) {   // rel: line L+rel
             if (rel >= 0) {
@@ -1683,15 +1726,22 @@ __global__ void __launch_bounds__(256) k_check(const uint8_t *__restrict__ text,
                                                unsigned long long item_cap, unsigned char *__restrict__ results, const ResolveCounters *ctr) {
     if (ctr->overflow) return;
     const unsigned long long n = ctr->n_items < item_cap ? ctr->n_items : item_cap;
+    PM_TR(3, ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, 0);
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
         const Item it = items[i];
+        PM_TR(3, i >> 5, 1);
         if (it.len == kItemInvalid) {
             results[i] = 0;
         } else if (it.len <= kLongLine) {
             UnitTables ut = unit_tables(blob, h, it.unit);
             results[i] = line_matches(text, it.a, it.a + it.len, ut);
         }
+        PM_TR(3, i >> 5, 2);
     }
+#ifdef PM_TRACE
+    __syncwarp();
+    PM_TR(3, ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, 3);
+#endif
 }
 
 // One warp walks one long line.  Lane i owns bytes [a + i*c, a + (i+1)*c).  Lane 0 starts in
@@ -2175,3 +2225,19 @@ cudaError_t launch_line_starts(const uint8_t *text, const unsigned long long *ti
 }
 
 }  // namespace pm
+
+#ifdef PM_TRACE
+// Debug builds only: copies the warp time stamps of the last launches to the host and clears them.
+extern "C" int pm_debug_trace_read(unsigned long long *out, unsigned long long n_words) {
+    const unsigned long long all = (unsigned long long)pm::kTraceRegions * pm::kTraceWarps * 8;
+    if (n_words > all) n_words = all;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(out, pm::g_trace, n_words * 8);
+    if (e == cudaSuccess) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, pm::g_trace);
+        if (e == cudaSuccess) e = cudaMemset(p, 0, all * 8);
+    }
+    return (int)e;
+}
+#endif
