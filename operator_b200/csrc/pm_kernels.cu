@@ -758,15 +758,22 @@ __device__ __forceinline__ void warp_touch_table(const uint16_t *tab, uint32_t b
 // its per-warp budget: a lookup then costs one shared-memory read, ~25 cycles, and never misses; through
 // L1 the same walk saw a 56 % hit rate, 48 warps per SM with a table each, and ~70 % of the kernel's
 // stall samples sat on these loads).
-template <bool TAB_SHARED>
+// TAB: 0 = `tab` is the table in global memory, 1 = the warp's copy in shared memory, 2 = the same with one byte per
+// entry (units of at most 256 states: twice the tables fit the warp's budget).
+template <int TAB>
 __device__ __forceinline__ uint32_t warp_walk_line(const uint8_t *__restrict__ text, unsigned long long a, unsigned long long b, const uint16_t *__restrict__ tab,
                                                    uint32_t stride, uint32_t acc, uint32_t dead, uint32_t mid, const uint8_t *__restrict__ gcm,
                                                    uint8_t *cmap_s, uint8_t *cls) {
     const int lane = threadIdx.x & 31;
     uint32_t s = 0;
-    const uint32_t tab_saddr = TAB_SHARED ? (uint32_t)__cvta_generic_to_shared(tab) : 0u;
+    const uint32_t tab_saddr = TAB ? (uint32_t)__cvta_generic_to_shared(tab) : 0u;
     auto next = [&](uint32_t st, uint32_t c) -> uint32_t {
-        if (TAB_SHARED) {
+        if (TAB == 2) {
+            uint32_t v;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(tab_saddr + (st * stride + c)));
+            return v;
+        }
+        if (TAB == 1) {
             unsigned short v;
             asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(tab_saddr + 2u * (st * stride + c)));
             return v;
@@ -870,13 +877,26 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
         // (opaque to the compiler from here on: otherwise it re-derives the pointer from the uniform base
         // and the 32-bit table offset inside every lookup, a 64-bit carry chain of five instructions)
         asm volatile("" : "+l"(gtab));
-        const uint32_t tbytes = (uint32_t)ud.nstates * ud.stride * 2u;
-        const bool staged = tbytes <= table_cap;   // warp-uniform
+        const uint32_t entries = (uint32_t)ud.nstates * ud.stride, tbytes = entries * 2u;
+        // (warp-uniform) one byte per entry where the state numbers allow it: most verify tables are 2-7 KiB, the budget 4 KiB
+        const bool staged8 = ud.nstates <= 256 && entries <= table_cap;
+        const bool staged = !staged8 && tbytes <= table_cap;
         unsigned char *stab = s_tables + (size_t)warp * table_cap;
         // a pattern that is nothing but its literal(s): k_confirm's comparison was the match, only the line start is
         // still needed (warp-uniform)
         const bool lit = ud.literal_is_match != 0;
         if (lit) {
+        } else if (staged8) {   // 8 entries per lane and step, all loads of the warp in flight together
+            __syncwarp();
+            const uint4 *gt = reinterpret_cast<const uint4 *>(gtab);
+#pragma unroll 4
+            for (uint32_t e = lane * 8u; e < entries; e += 256u) {
+                const uint4 q = __ldg(gt + (e >> 3));
+                uint2 o;
+                o.x = __byte_perm(q.x, q.y, 0x6420);
+                o.y = __byte_perm(q.z, q.w, 0x6420);
+                *reinterpret_cast<uint2 *>(stab + e) = o;
+            }
         } else if (staged) {   // tables start 16-byte aligned in the blob and are followed by at least their padding
             __syncwarp();
             for (uint32_t off = lane * 16u; off < tbytes; off += 512u)
@@ -945,14 +965,16 @@ __global__ void __launch_bounds__(kVerifyWarps * 32, 12) k_verify(const uint8_t 
         }
         const unsigned long long lend = strip_cr(text, pt, ls, le);
         // ---- the walk (class map and first piece of the line travel together)
-        uint32_t st = staged ? warp_walk_line<true>(text, ls, lend, reinterpret_cast<const uint16_t *>(stab), stride, acc, ud.dead_state, ud.mid_state,
-                                                    blob + h.off_classmaps + ud.classmap_off, s_cmap[warp], s_cls[warp])
-                             : warp_walk_line<false>(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, blob + h.off_classmaps + ud.classmap_off,
-                                                     s_cmap[warp], s_cls[warp]);
+        const uint8_t *gcm = blob + h.off_classmaps + ud.classmap_off;
+        uint32_t st = staged8  ? warp_walk_line<2>(text, ls, lend, reinterpret_cast<const uint16_t *>(stab), stride, acc, ud.dead_state, ud.mid_state, gcm,
+                                                   s_cmap[warp], s_cls[warp])
+                      : staged ? warp_walk_line<1>(text, ls, lend, reinterpret_cast<const uint16_t *>(stab), stride, acc, ud.dead_state, ud.mid_state, gcm,
+                                                   s_cmap[warp], s_cls[warp])
+                               : warp_walk_line<0>(text, ls, lend, gtab, stride, acc, ud.dead_state, ud.mid_state, gcm, s_cmap[warp], s_cls[warp]);
         if (st != acc) st = __ldg(gtab + (st * stride + stride - 1));
         PM_TR(1, i, 4);
         PM_TV(1, i, 6, lend - ls);
-        PM_TV(1, i, 7, ((unsigned long long)tbytes << 1) | (staged ? 1u : 0u));
+        PM_TV(1, i, 7, ((unsigned long long)tbytes << 1) | ((staged || staged8) ? 1u : 0u));
         if (lane == 0) {
             if (st == acc) {
                 unsigned long long at = atomicAdd(&ctr->n_raw, 1ull);

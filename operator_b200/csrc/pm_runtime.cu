@@ -308,6 +308,12 @@ constexpr size_t kCtrBytes = sizeof(ScanCounters) + 16 + sizeof(ResolveCounters)
 
 size_t round_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// PM_VERIFY_SMEM_ALWAYS=1: k_verify stages tables in shared memory also with several batches in flight (measurement switch)
+bool verify_smem_always() {
+    static const bool v = getenv("PM_VERIFY_SMEM_ALWAYS") != nullptr;
+    return v;
+}
+
 // PM_TEST_TINY_QUEUES=1 starts every internal queue (filter candidates, raw events, resolve work
 // items) at a few entries, so that the overflow -> grow -> rerun paths run on small test inputs.
 bool tiny_queues() {
@@ -853,7 +859,7 @@ int scan_async(pm_batch *b) {
         CU(cudaMemcpyAsync(w.h_pods.p, w.pods_dev.p, sizeof(PodDev) * np, cudaMemcpyDeviceToHost, w.stream2));
         CU(cudaEventRecord(w.pods_copied, w.stream2));
         CU(launch_confirm(w.text.as<uint8_t>(), w.total, dl, w.table(), w.cand.as<unsigned long long>(), w.cand_cap, w.tasks.as<unsigned long long>(),
-                          w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), w.sms_post, w.stream, /*tables_in_smem=*/d->depth == 1));
+                          w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), w.sms_post, w.stream, /*tables_in_smem=*/d->depth == 1 || verify_smem_always()));
         w.launches += 1 + 2 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
         w.mark("k_verify");
         CU(cudaEventRecord(w.e[8], w.stream));
@@ -1346,12 +1352,17 @@ int pm_library_publish(pm_ctx *ctx, pm_library *l) {
                     l->dev[d].stack_first = sf;
                 }
                 // k_verify copies a task's table into shared memory when it fits the per-warp budget: the largest
-                // table among the filtered primaries, capped so that 4 warps x budget + 3 KiB still lets 11-12 CTAs share an SM
+                // table among the filtered primaries that still walk (one byte per entry up to 256 states), capped at 8 KiB: 4 warps x
+                // budget + 3 KiB then still lets 6 CTAs share an SM, and since the literal-only patterns stopped walking the kernel no
+                // longer needs more (4 KiB left 8 % of the walks on the L1 path, 15 us each: they set the kernel's time)
                 const UnitDesc *udv = reinterpret_cast<const UnitDesc *>(hb + bh.off_units);
                 uint32_t cap = 0;
                 for (uint32_t i = 0; i < bh.n_patterns; i++)
-                    if (pdv[i].tier == 1 && !udv[pdv[i].unit].literal_is_match) cap = std::max(cap, (uint32_t)udv[pdv[i].unit].nstates * udv[pdv[i].unit].stride * 2u);
-                static const uint32_t cap_max = getenv("PM_VERIFY_TABLE_CAP") ? (uint32_t)atoi(getenv("PM_VERIFY_TABLE_CAP")) : 4096u;
+                    if (pdv[i].tier == 1 && !udv[pdv[i].unit].literal_is_match) {   // one byte per entry up to 256 states (k_verify)
+                        const UnitDesc &u = udv[pdv[i].unit];
+                        cap = std::max(cap, (uint32_t)u.nstates * u.stride * (u.nstates <= 256 ? 1u : 2u));
+                    }
+                static const uint32_t cap_max = getenv("PM_VERIFY_TABLE_CAP") ? (uint32_t)atoi(getenv("PM_VERIFY_TABLE_CAP")) : 8192u;
                 l->dev[d].verify_table_cap = std::min((cap + 255u) & ~255u, cap_max);
             }
         }
