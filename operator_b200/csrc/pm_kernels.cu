@@ -205,6 +205,11 @@ __device__ __forceinline__ uint32_t shr_wrap(uint32_t v, uint32_t amount) {     
     asm("shf.r.wrap.b32 %0, %1, 0, %2;" : "=r"(r) : "r"(v), "r"(amount));
     return r;
 }
+__device__ __forceinline__ uint32_t lds_u8(uint32_t saddr) {
+    uint32_t r;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r) : "r"(saddr));
+    return r;
+}
 __device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
     uint32_t r;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(saddr));
@@ -1513,6 +1518,12 @@ struct Item {
     uint32_t unit;
 };
 
+struct Group {                           // a run of items that share a unit: the STACK run of an event, or one secondary's window
+    unsigned long long first;            // index of the run's first item
+    uint32_t count;
+    uint32_t unit;
+};
+
 struct EvAux {                           // what k_plan learns about one key, indexed like keys[] (64 bytes)
     unsigned long long item_base;
     int32_t n_stack, na;
@@ -1597,7 +1608,7 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
                                                           unsigned long long key_cap,
                                                           Item *__restrict__ items, unsigned long long item_cap, uint32_t *__restrict__ long_list,
                                                           unsigned long long long_cap, EvAux *__restrict__ aux, ResolveCounters *ctr, int slots,
-                                                          const StackFirst stack_first) {
+                                                          const StackFirst stack_first, Group *__restrict__ groups, unsigned long long group_cap) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned long long *fwd = reinterpret_cast<unsigned long long *>(smem_raw) + (size_t)warp * 2 * slots;   // fwd[i]: '\n' that ends line L+i
@@ -1680,10 +1691,20 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
         unsigned long long base = 0;
         if (lane == 0 && n_items) base = atomicAdd(&ctr->n_items, n_items);
         base = __shfl_sync(FULL, base, 0);
-        const bool fits = base + n_items <= item_cap;
+        // the items come in runs that share a unit (the STACK run, one window per secondary): k_check takes a warp per run
+        // (at most 32 items per run, one per lane of k_check's warp: longer runs are cut)
+        const uint32_t stack_grp = ((uint32_t)n_stack + 31u) / 32u;
+        uint32_t n_grp = stack_grp;
+        for (uint32_t j = 0; j < pd.sec_count; j++) n_grp += (2u * (uint32_t)sds[pd.sec_first + j].window + 1u + 31u) / 32u;
+        unsigned gbase = 0;
+        if (lane == 0 && n_grp) gbase = atomicAdd(&ctr->n_groups, n_grp);
+        gbase = __shfl_sync(FULL, gbase, 0);
+        const bool fits = base + n_items <= item_cap && (unsigned long long)gbase + n_grp <= group_cap;
         if (!fits && lane == 0) ctr->overflow = 1;
 
         if (fits) {
+            if ((uint32_t)lane < stack_grp) groups[gbase + lane] = Group{base + 32ull * lane, min(32u, (uint32_t)n_stack - 32u * lane), h.stack_unit};
+            unsigned gnext = gbase + stack_grp;
             // STACK items: lines L+na+1 .. L+stack_cap
             for (int k = lane; k < n_stack; k += 32) {
                 unsigned long long a, b;
@@ -1700,6 +1721,9 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
             for (uint32_t j = 0; j < pd.sec_count; j++) {
                 const SecDesc sd = sds[pd.sec_first + j];
                 const int cnt = 2 * sd.window + 1;
+                const uint32_t pieces = ((uint32_t)cnt + 31u) / 32u;
+                for (uint32_t q = lane; q < pieces; q += 32) groups[gnext + q] = Group{off + 32ull * q, min(32u, (uint32_t)cnt - 32u * q), sd.unit};
+                gnext += pieces;
                 for (int idx = lane; idx < cnt; idx += 32) {
                     int d = (idx + 1) >> 1;
                     int rel = (idx & 1) ? -d : d;
@@ -1744,26 +1768,117 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
     }
 }
 
-__global__ void __launch_bounds__(256) k_check(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h, const Item *__restrict__ items,
-                                               unsigned long long item_cap, unsigned char *__restrict__ results, const ResolveCounters *ctr) {
-    if (ctr->overflow) return;
-    const unsigned long long n = ctr->n_items < item_cap ? ctr->n_items : item_cap;
-    PM_TR(3, ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, 0);
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
-        const Item it = items[i];
-        PM_TR(3, i >> 5, 1);
-        if (it.len == kItemInvalid) {
-            results[i] = 0;
-        } else if (it.len <= kLongLine) {
-            UnitTables ut = unit_tables(blob, h, it.unit);
-            results[i] = line_matches(text, it.a, it.a + it.len, ut);
+// One thread walks one line [a, b) through the warp's shared-memory copy of a unit's table (one byte per entry) and class
+// map, then feeds END-OF-LINE.  The text comes in aligned 16-byte pieces; the class of every byte of a piece is looked up
+// before the walk, so that what remains per byte is one multiply-add and one shared-memory read.
+__device__ __forceinline__ bool line_matches_staged(const uint8_t *__restrict__ text, unsigned long long a, unsigned long long b, const uint8_t *tab,
+                                                    const uint8_t *cm, uint32_t stride, uint32_t acc, uint32_t dead, unsigned long long tr_group = 0) {
+    uint32_t s = 0;
+    const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(tab);
+    unsigned long long p = a & ~15ull;
+#ifdef PM_TRACE
+    const long long tr_c0 = clock64();
+    const unsigned long long tr_p0 = p;
+#endif
+    {   // The lanes walk 32 different lines that were last touched by k_plan: a piece load of the warp waits for the slowest of
+        // 32 separate L2/DRAM accesses, ~2 000 cycles where the 16 lookups it feeds take 650 (tools_warp_trace.py).  So every
+        // lane asks for its whole line first (at most nine 32-byte sectors), all at once and none waited for.
+        uint32_t sink = 0;
+        for (unsigned long long q = (a & ~31ull) + 32; q < b; q += 32) sink ^= __ldg(reinterpret_cast<const uint32_t *>(text + q));
+        asm volatile("" ::"r"(sink));
+    }
+    uint4 v = *reinterpret_cast<const uint4 *>(text + p);
+    for (; p < b && s != acc && s != dead; p += 16) {
+        const uint32_t x[4] = {v.x, v.y, v.z, v.w};
+        // the next piece is requested before this one is walked: the lanes walk 32 different lines and cross into new cache
+        // lines at different steps, so nearly every piece load of the warp has some lane waiting for L2 or DRAM
+        if (p + 16 < b) v = *reinterpret_cast<const uint4 *>(text + p + 16);
+        uint32_t c[16];   // the column of each byte as a shared-memory address: the row offset is all the walk adds
+#pragma unroll
+        for (int j = 0; j < 16; j++) c[j] = tab_s + cm[(x[j >> 2] >> (8 * (j & 3))) & 0xFFu];
+        // ONE code path for whole and partial pieces (bytes outside the line are looked up like the others and the result
+        // dropped): the lanes are at different places of their lines, and with a separate path for the first and last piece
+        // the warp ran both paths in nearly every iteration - 2 000 cycles per piece instead of 700
+        const int lo = p >= a ? 0 : (int)(a - p), hi = p + 16 <= b ? 16 : (int)(b - p);
+        const uint32_t valid = (0xFFFFu >> (16 - hi)) & (0xFFFFu << lo);
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const uint32_t nx = lds_u8(s * stride + c[j]);
+            s = ((valid >> j) & 1u) ? nx : s;
         }
-        PM_TR(3, i >> 5, 2);
     }
 #ifdef PM_TRACE
-    __syncwarp();
-    PM_TR(3, ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, 3);
+    if ((threadIdx.x & 31) == 0) {
+        PM_TV(3, tr_group, 4, (unsigned long long)(clock64() - tr_c0));
+        PM_TV(3, tr_group, 5, (p - tr_p0) / 16);
+    }
 #endif
+    if (s == acc) return true;
+    if (s == dead) return false;
+    return tab[s * stride + stride - 1] == acc;
+}
+
+// The context lines of the events: one WARP per run of items that share a unit (k_plan's groups), one lane per line.
+// A line walk is a chain of dependent table reads; with the tables in global memory a step cost ~130 cycles (the 32
+// lanes of a warp stand in different rows and columns of a 256-column table: several L1 lines per step, and the warps
+// of an SM do not share tables), 15 us for the longest line of a warp (tools_warp_trace.py).  So the warp first copies its
+// unit's table - one byte per entry, which every unit with at most 256 states allows - and class map into shared memory.
+constexpr uint32_t kCheckTabCap = 1536;   // table entries a warp can stage
+constexpr int kCheckWarps = 8;
+
+__global__ void __launch_bounds__(kCheckWarps * 32) k_check(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
+                                                           const Item *__restrict__ items, const Group *__restrict__ groups, unsigned long long group_cap,
+                                                           unsigned char *__restrict__ results, const ResolveCounters *ctr) {
+    __shared__ __align__(16) uint8_t s_cm[kCheckWarps][256];
+    __shared__ __align__(16) uint8_t s_tb[kCheckWarps][kCheckTabCap];
+    if (ctr->overflow) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned long long n = ctr->n_groups < group_cap ? ctr->n_groups : group_cap;
+    const UnitDesc *units = reinterpret_cast<const UnitDesc *>(blob + h.off_units);
+    PM_TR(3, (unsigned long long)blockIdx.x * kCheckWarps + warp, 0);
+    for (unsigned long long g = (unsigned long long)blockIdx.x * kCheckWarps + warp; g < n; g += (unsigned long long)gridDim.x * kCheckWarps) {
+        const Group gr = groups[g];
+        Item it{0, kItemInvalid, 0};
+        if ((uint32_t)lane < gr.count) it = items[gr.first + lane];   // under the table copy
+        const UnitDesc ud = units[gr.unit];
+        PM_TR(3, g, 1);
+        const uint32_t entries = (uint32_t)ud.nstates * ud.stride;
+        const bool staged = ud.nstates <= 256 && entries <= kCheckTabCap;   // warp-uniform
+        __syncwarp();   // the previous run's walks are over
+        if (staged) {
+            const uint32_t *gcm = reinterpret_cast<const uint32_t *>(blob + h.off_classmaps + ud.classmap_off);
+            reinterpret_cast<uint32_t *>(s_cm[warp])[lane] = __ldg(gcm + lane);
+            reinterpret_cast<uint32_t *>(s_cm[warp])[32 + lane] = __ldg(gcm + 32 + lane);
+            // tables start 16-byte aligned in the blob and are followed by at least their padding: 8 entries per lane and step
+            const uint4 *gt = reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off);
+#pragma unroll 2
+            for (uint32_t e = lane * 8u; e < entries; e += 256u) {
+                const uint4 q = __ldg(gt + (e >> 3));
+                uint2 o;
+                o.x = __byte_perm(q.x, q.y, 0x6420);
+                o.y = __byte_perm(q.z, q.w, 0x6420);
+                *reinterpret_cast<uint2 *>(s_tb[warp] + e) = o;
+            }
+            __syncwarp();
+        }
+        PM_TR(3, g, 2);
+        if ((uint32_t)lane < gr.count) {   // a run has at most 32 items (k_plan)
+            const unsigned long long i = gr.first + lane;
+            if (it.len == kItemInvalid) {
+                results[i] = 0;
+            } else if (it.len <= kLongLine) {
+                if (staged) {
+                    results[i] = line_matches_staged(text, it.a, it.a + it.len, s_tb[warp], s_cm[warp], ud.stride, ud.accept_state, ud.dead_state, g);
+                } else {
+                    UnitTables ut = unit_tables(blob, h, it.unit);
+                    results[i] = line_matches(text, it.a, it.a + it.len, ut);
+                }
+            }
+        }
+        PM_TR(3, g, 3);
+        PM_TV(3, g, 6, ((unsigned long long)entries << 1) | (staged ? 1u : 0u));
+        PM_TV(3, g, 7, gr.count);
+    }
 }
 
 // One warp walks one long line.  Lane i owns bytes [a + i*c, a + (i+1)*c).  Lane 0 starts in
@@ -2083,6 +2198,9 @@ cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, 
         cudaError_t e = cudaFuncSetAttribute(k_verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsm);
         if (e != cudaSuccess) return e;
     }
+    // with tables in shared memory the kernel wants all the shared memory an SM has (6 CTAs of 35 KiB); without the hint the
+    // driver's L1/shared split left room for fewer and the kernel ran in waves
+    cudaFuncSetAttribute(k_verify, cudaFuncAttributePreferredSharedMemoryCarveout, vsm ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault);
     k_verify<<<num_sms * 16, kVerifyWarps * 32, vsm, s>>>(text, total_bytes, lib.blob, lib.h, pt, tasks, raw_cap, raw, raw_cap, ctr, table_cap);
     return cudaGetLastError();
 }
@@ -2134,6 +2252,7 @@ cudaError_t launch_gram_profile(const uint8_t *text, unsigned long long sample_b
 
 size_t resolve_item_bytes() { return sizeof(Item); }
 size_t resolve_aux_bytes() { return sizeof(EvAux); }
+size_t resolve_group_bytes() { return sizeof(Group); }
 
 cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const unsigned long long *tile_prefix, PodTable pt,
                            const unsigned long long *keys, const unsigned long long *n_keys_dev, unsigned long long key_cap,
@@ -2153,7 +2272,8 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
         if (e != cudaSuccess) return e;
     }
     k_plan<<<blocks, kPlanWarps * 32, plan_smem, s>>>(text, lib.blob, lib.h, tile_prefix, pt, keys, n_keys_dev, key_cap, items, rs.item_cap,
-                                                      rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots, lib.stack_first);
+                                                      rs.long_list, rs.long_cap, reinterpret_cast<EvAux *>(rs.aux), rs.ctr, slots, lib.stack_first,
+                                                      reinterpret_cast<Group *>(rs.groups), rs.group_cap);
     stage_mark("k_plan");
     // short and long lines are independent: walk them concurrently when a side stream is given.  (Both in one
     // launch, the long lines on warp_walk_line in the first CTAs of the grid, was measured in round 2: 47 us
@@ -2163,9 +2283,15 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
         cudaEventRecord(fork_ev, s);
         cudaStreamWaitEvent(side, fork_ev, 0);
     }
+    {   // k_check wants five CTAs of 14 KiB per SM, k_check_long (no shared memory) runs beside it: the same L1/shared split for
+        // both, or an SM has to drain the CTAs of one before it can take CTAs of the other (half of k_check's CTAs started 11 us
+        // late, tools_warp_trace.py)
+        cudaFuncSetAttribute(k_check, cudaFuncAttributePreferredSharedMemoryCarveout, 40);
+        cudaFuncSetAttribute(k_check_long, cudaFuncAttributePreferredSharedMemoryCarveout, 40);
+    }
     k_check_long<<<num_sms * 16, 128, 0, fork ? side : s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
     if (fork) cudaEventRecord(join_ev, side);
-    k_check<<<num_sms * 8, 256, 0, s>>>(text, lib.blob, lib.h, items, rs.item_cap, rs.results, rs.ctr);
+    k_check<<<num_sms * 5, kCheckWarps * 32, 0, s>>>(text, lib.blob, lib.h, items, reinterpret_cast<const Group *>(rs.groups), rs.group_cap, rs.results, rs.ctr);
     stage_mark("k_check");
     if (fork) cudaStreamWaitEvent(s, join_ev, 0);
     stage_mark("join k_check_long");

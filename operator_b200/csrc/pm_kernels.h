@@ -110,10 +110,10 @@ size_t sort_temp_bytes(unsigned long long n);
 cudaError_t launch_sort_unique(unsigned long long *raw, unsigned long long *sorted, unsigned long long *uniq,
                                unsigned long long n, unsigned long long *n_unique, void *temp, size_t temp_bytes, cudaStream_t s);
 // Resolve stage scratch (device memory owned by the caller).  items: item_cap x resolve_item_bytes(),
-// results: item_cap bytes, long_list: long_cap u32, aux: n_events x resolve_aux_bytes().
+// results: item_cap bytes, long_list: long_cap u32, aux: n_events x resolve_aux_bytes(), groups: group_cap x resolve_group_bytes().
 struct ResolveCounters {
     unsigned long long n_items, n_long;
-    unsigned int overflow, pad;
+    unsigned int overflow, n_groups;
 };
 struct ResolveScratch {
     void *items;
@@ -123,7 +123,10 @@ struct ResolveScratch {
     unsigned long long long_cap;
     void *aux;
     ResolveCounters *ctr;
+    void *groups;                       // group_cap x resolve_group_bytes(): runs of items that share a unit (k_check: a warp per run)
+    unsigned long long group_cap;
 };
+size_t resolve_group_bytes();
 size_t resolve_item_bytes();
 size_t resolve_aux_bytes();
 // Four launches (k_plan, k_check, k_check_long, k_finalize).  If rs.ctr->overflow is set afterwards the

@@ -265,9 +265,9 @@ struct DevWork {
     uint64_t total = 0, n_tiles = 0;
     uint64_t cand_cap = 0, raw_cap = 0;
     Buf text, tile_nl, tile_prefix, scratch, cand, raw, sorted, uniq, temp, ctr, pods_dev, ev_soa, lines_tmp;
-    Buf rs_items, rs_results, rs_long, rs_aux;   // resolve-stage scratch
+    Buf rs_items, rs_results, rs_long, rs_aux, rs_groups;   // resolve-stage scratch
     Buf tasks, sort_scratch;
-    uint64_t item_cap = 0, long_cap = 0, ev_cap = 0;
+    uint64_t item_cap = 0, long_cap = 0, ev_cap = 0, group_cap = 0;
     int any_trailing_cr = 0;
     PodTable table() const { return PodTable{pods_dev.as<PodDev>(), (int)pods.size(), any_trailing_cr}; }
     Buf h_ctr, h_pods, h_soa;   // pinned mirrors
@@ -359,7 +359,7 @@ void release_work(pm_batch *b) {
         Device *d = b->ctx->devs[w.slot];
         cudaSetDevice(d->id);
         if (w.stream) cudaStreamSynchronize(w.stream);
-        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.tasks, &w.sort_scratch})
+        for (Buf *x : {&w.text, &w.tile_nl, &w.tile_prefix, &w.scratch, &w.cand, &w.raw, &w.sorted, &w.uniq, &w.temp, &w.ctr, &w.pods_dev, &w.ev_soa, &w.lines_tmp, &w.rs_items, &w.rs_results, &w.rs_long, &w.rs_aux, &w.rs_groups, &w.tasks, &w.sort_scratch})
             put(d->pool, *x);
         for (Buf *x : {&w.h_ctr, &w.h_pods, &w.h_soa}) put(b->ctx->pinned, *x);
         if (w.stream) {
@@ -763,6 +763,10 @@ int ensure_resolve_scratch(pm_batch *b, DevWork &w, uint64_t ev_cap) {
     if ((rc = get(d->pool, w.item_cap * resolve_item_bytes(), w.rs_items))) return rc;
     if ((rc = get(d->pool, w.item_cap, w.rs_results))) return rc;
     if ((rc = get(d->pool, w.long_cap * 4, w.rs_long))) return rc;
+    // runs of items that share a unit (one STACK run and one window per secondary and event): a run has at least one item,
+    // most have 3-25; too few is an overflow like any other and grows with item_cap
+    w.group_cap = tiny_queues() ? std::max<uint64_t>(w.group_cap, 4) : std::max<uint64_t>(w.group_cap, w.item_cap / 4 + (1u << 12));
+    if ((rc = get(d->pool, w.group_cap * resolve_group_bytes(), w.rs_groups))) return rc;
     // the resolve stage plans either the sorted events (<= ev_cap) or the raw queue (<= kMediumSort)
     w.key_cap = std::max<uint64_t>(ev_cap, std::min<uint64_t>(w.raw_cap, kMediumSort));
     if ((rc = get(d->pool, w.key_cap * resolve_aux_bytes(), w.rs_aux))) return rc;
@@ -777,7 +781,7 @@ int enqueue_resolve(pm_batch *b, DevWork &w, bool from_raw = false) {
     w.hook_marks();
     SoaLayout L(w.ev_cap);
     ResolveScratch rs{w.rs_items.p, w.item_cap, w.rs_results.as<unsigned char>(), w.rs_long.as<uint32_t>(), w.long_cap, w.rs_aux.p,
-                      reinterpret_cast<ResolveCounters *>(w.ctr.as<char>() + kOffResolve)};
+                      reinterpret_cast<ResolveCounters *>(w.ctr.as<char>() + kOffResolve), w.rs_groups.p, w.group_cap};
     const unsigned long long *n_unique = reinterpret_cast<const unsigned long long *>(w.ctr.as<char>() + kOffUnique);
     const unsigned long long *keys = from_raw ? w.raw.as<unsigned long long>() : w.uniq.as<unsigned long long>();
     const unsigned long long *n_keys = from_raw ? &w.ctr.as<ScanCounters>()->n_raw : n_unique;
@@ -952,6 +956,7 @@ int finish(pm_batch *b, pm_result_view *out) {
             } else {
                 w.item_cap = std::min<uint64_t>(w.item_cap * 4, 0xFFFFFFF0ull);
                 w.long_cap *= 4;
+                w.group_cap *= 4;
                 if ((rc = ensure_resolve_scratch(b, w, w.ev_cap))) return rc;
             }
             if ((rc = enqueue_resolve(b, w))) return rc;

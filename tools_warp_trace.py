@@ -23,7 +23,7 @@ from operator_b200 import engine as _engine
 REGIONS = {0: ("k_confirm", ["enter", "candidate read", "exit"]),
            1: ("k_verify", ["enter", "task read", "line bytes here", "line bounds + tables", "walk done", "literal-only: emit"]),
            2: ("k_plan", ["enter", "loop", "key + pattern + pod", "line number", "forward lines", "backward lines"]),
-           3: ("k_check", ["enter", "item read", "lane 0 done", "warp done"])}
+           3: ("k_check", ["enter", "group read", "table staged", "lines walked"])}
 WARPS = 16384
 
 
@@ -73,6 +73,8 @@ def main():
         x = x.copy()
         vals = x[:, 6:].copy()
         x[:, 6:] = 0
+        if name == "k_check":
+            x[:, 4:6] = 0
         t0 = x[x > 0].min()
         out = {"kernel": name, "warps_entered": int(seen.sum()), "kernel_span_us": round(float(x.max() - t0) / 1e3, 2),
                "enter": pct((x[seen, 0] - t0) / 1e3)}
@@ -97,6 +99,17 @@ def main():
             for nm, sel in (("staged", staged), ("through L1", ~staged)):
                 if sel.any():
                     out["walk us, " + nm] = pct(dt[sel])
+        if name == "k_check":
+            grp = vals[:, 1] > 0
+            if grp.any():
+                ent, st = vals[grp, 0] >> 1, (vals[grp, 0] & 1) == 1
+                out["groups"] = int(grp.sum())
+                out["group: items"] = pct(vals[grp, 1])
+                out["group: table entries"] = pct(ent)
+                out["group: table in shared memory"] = "%d of %d" % (int(st.sum()), int(grp.sum()))
+                w = (t[reg][:, 5] > 0)
+                out["lane 0: pieces"] = pct(t[reg][w, 5])
+                out["lane 0: cycles per piece"] = pct(t[reg][w, 4] / np.maximum(t[reg][w, 5], 1))
         print(json.dumps(out))
     b.release()
     pinned.free()
