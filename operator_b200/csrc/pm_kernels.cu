@@ -1771,9 +1771,8 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan(const uint8_t *__restr
 // One thread walks one line [a, b) through the warp's shared-memory copy of a unit's table (one byte per entry) and class
 // map, then feeds END-OF-LINE.  The text comes in aligned 16-byte pieces; the class of every byte of a piece is looked up
 // before the walk, so that what remains per byte is one multiply-add and one shared-memory read.
-__device__ __forceinline__ bool line_matches_staged(const uint8_t *__restrict__ text, unsigned long long a, unsigned long long b, const uint8_t *tab,
-                                                    const uint8_t *cm, uint32_t stride, uint32_t acc, uint32_t dead, unsigned long long tr_group = 0) {
-    uint32_t s = 0;
+__device__ __forceinline__ uint32_t walk_staged(const uint8_t *__restrict__ text, unsigned long long a, unsigned long long b, uint32_t s, const uint8_t *tab,
+                                                const uint8_t *cm, uint32_t stride, uint32_t acc, uint32_t dead, unsigned long long tr_group = ~0ull) {
     const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(tab);
     unsigned long long p = a & ~15ull;
 #ifdef PM_TRACE
@@ -1782,7 +1781,7 @@ __device__ __forceinline__ bool line_matches_staged(const uint8_t *__restrict__ 
 #endif
     {   // The lanes walk 32 different lines that were last touched by k_plan: a piece load of the warp waits for the slowest of
         // 32 separate L2/DRAM accesses, ~2 000 cycles where the 16 lookups it feeds take 650 (tools_warp_trace.py).  So every
-        // lane asks for its whole line first (at most nine 32-byte sectors), all at once and none waited for.
+        // lane asks for its whole range first (at most nine 32-byte sectors), all at once and none waited for.
         uint32_t sink = 0;
         for (unsigned long long q = (a & ~31ull) + 32; q < b; q += 32) sink ^= __ldg(reinterpret_cast<const uint32_t *>(text + q));
         asm volatile("" ::"r"(sink));
@@ -1796,7 +1795,7 @@ __device__ __forceinline__ bool line_matches_staged(const uint8_t *__restrict__ 
         uint32_t c[16];   // the column of each byte as a shared-memory address: the row offset is all the walk adds
 #pragma unroll
         for (int j = 0; j < 16; j++) c[j] = tab_s + cm[(x[j >> 2] >> (8 * (j & 3))) & 0xFFu];
-        // ONE code path for whole and partial pieces (bytes outside the line are looked up like the others and the result
+        // ONE code path for whole and partial pieces (bytes outside the range are looked up like the others and the result
         // dropped): the lanes are at different places of their lines, and with a separate path for the first and last piece
         // the warp ran both paths in nearly every iteration - 2 000 cycles per piece instead of 700
         const int lo = p >= a ? 0 : (int)(a - p), hi = p + 16 <= b ? 16 : (int)(b - p);
@@ -1808,14 +1807,43 @@ __device__ __forceinline__ bool line_matches_staged(const uint8_t *__restrict__ 
         }
     }
 #ifdef PM_TRACE
-    if ((threadIdx.x & 31) == 0) {
+    if ((threadIdx.x & 31) == 0 && tr_group != ~0ull) {
         PM_TV(3, tr_group, 4, (unsigned long long)(clock64() - tr_c0));
         PM_TV(3, tr_group, 5, (p - tr_p0) / 16);
     }
 #endif
+    return s;
+}
+
+__device__ __forceinline__ bool line_matches_staged(const uint8_t *__restrict__ text, unsigned long long a, unsigned long long b, const uint8_t *tab,
+                                                    const uint8_t *cm, uint32_t stride, uint32_t acc, uint32_t dead, unsigned long long tr_group = ~0ull) {
+    const uint32_t s = walk_staged(text, a, b, 0, tab, cm, stride, acc, dead, tr_group);
     if (s == acc) return true;
     if (s == dead) return false;
     return tab[s * stride + stride - 1] == acc;
+}
+
+// The warp's copy of a unit's table (one byte per entry) and class map in shared memory; false if the unit has more than 256
+// states or more entries than the budget.  Tables start 16-byte aligned in the blob and are followed by at least their padding.
+constexpr uint32_t kCheckTabCap = 1536;   // table entries a warp can stage (the context units of a crash-log library have 150-1400)
+__device__ __forceinline__ bool warp_stage_unit(const uint8_t *__restrict__ blob, const BlobHeader &h, const UnitDesc &ud, uint8_t *cm_s, uint8_t *tb_s) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t entries = (uint32_t)ud.nstates * ud.stride;
+    if (ud.nstates > 256 || entries > kCheckTabCap) return false;   // warp-uniform
+    const uint32_t *gcm = reinterpret_cast<const uint32_t *>(blob + h.off_classmaps + ud.classmap_off);
+    reinterpret_cast<uint32_t *>(cm_s)[lane] = __ldg(gcm + lane);
+    reinterpret_cast<uint32_t *>(cm_s)[32 + lane] = __ldg(gcm + 32 + lane);
+    const uint4 *gt = reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off);
+#pragma unroll 2
+    for (uint32_t e = lane * 8u; e < entries; e += 256u) {   // 8 entries per lane and step
+        const uint4 q = __ldg(gt + (e >> 3));
+        uint2 o;
+        o.x = __byte_perm(q.x, q.y, 0x6420);
+        o.y = __byte_perm(q.z, q.w, 0x6420);
+        *reinterpret_cast<uint2 *>(tb_s + e) = o;
+    }
+    __syncwarp();
+    return true;
 }
 
 // The context lines of the events: one WARP per run of items that share a unit (k_plan's groups), one lane per line.
@@ -1823,7 +1851,6 @@ __device__ __forceinline__ bool line_matches_staged(const uint8_t *__restrict__ 
 // lanes of a warp stand in different rows and columns of a 256-column table: several L1 lines per step, and the warps
 // of an SM do not share tables), 15 us for the longest line of a warp (tools_warp_trace.py).  So the warp first copies its
 // unit's table - one byte per entry, which every unit with at most 256 states allows - and class map into shared memory.
-constexpr uint32_t kCheckTabCap = 1536;   // table entries a warp can stage
 constexpr int kCheckWarps = 8;
 
 __global__ void __launch_bounds__(kCheckWarps * 32) k_check(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h,
@@ -1843,24 +1870,9 @@ __global__ void __launch_bounds__(kCheckWarps * 32) k_check(const uint8_t *__res
         const UnitDesc ud = units[gr.unit];
         PM_TR(3, g, 1);
         const uint32_t entries = (uint32_t)ud.nstates * ud.stride;
-        const bool staged = ud.nstates <= 256 && entries <= kCheckTabCap;   // warp-uniform
+        (void)entries;
         __syncwarp();   // the previous run's walks are over
-        if (staged) {
-            const uint32_t *gcm = reinterpret_cast<const uint32_t *>(blob + h.off_classmaps + ud.classmap_off);
-            reinterpret_cast<uint32_t *>(s_cm[warp])[lane] = __ldg(gcm + lane);
-            reinterpret_cast<uint32_t *>(s_cm[warp])[32 + lane] = __ldg(gcm + 32 + lane);
-            // tables start 16-byte aligned in the blob and are followed by at least their padding: 8 entries per lane and step
-            const uint4 *gt = reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(blob + h.off_tables) + ud.table_off);
-#pragma unroll 2
-            for (uint32_t e = lane * 8u; e < entries; e += 256u) {
-                const uint4 q = __ldg(gt + (e >> 3));
-                uint2 o;
-                o.x = __byte_perm(q.x, q.y, 0x6420);
-                o.y = __byte_perm(q.z, q.w, 0x6420);
-                *reinterpret_cast<uint2 *>(s_tb[warp] + e) = o;
-            }
-            __syncwarp();
-        }
+        const bool staged = warp_stage_unit(blob, h, ud, s_cm[warp], s_tb[warp]);   // warp-uniform
         PM_TR(3, g, 2);
         if ((uint32_t)lane < gr.count) {   // a run has at most 32 items (k_plan)
             const unsigned long long i = gr.first + lane;
@@ -1890,19 +1902,25 @@ __global__ void __launch_bounds__(kCheckWarps * 32) k_check(const uint8_t *__res
 __global__ void __launch_bounds__(128) k_check_long(const uint8_t *__restrict__ text, const uint8_t *__restrict__ blob, BlobHeader h, const Item *__restrict__ items,
                                                     const uint32_t *__restrict__ long_list, unsigned long long long_cap, unsigned char *__restrict__ results,
                                                     const ResolveCounters *ctr) {
+    __shared__ __align__(16) uint8_t s_cm[4][256];
+    __shared__ __align__(16) uint8_t s_tb[4][kCheckTabCap];
     if (ctr->overflow) return;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned long long n = ctr->n_long < long_cap ? ctr->n_long : long_cap;
     const unsigned long long n_warps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
     for (unsigned long long k = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < n; k += n_warps) {
         const uint32_t idx = long_list[k];
         const Item it = items[idx];
         UnitTables ut = unit_tables(blob, h, it.unit);
+        __syncwarp();   // the previous line's walks are over
+        // like k_check: the unit's table and class map in shared memory where they fit (one byte per entry)
+        const bool staged = warp_stage_unit(blob, h, reinterpret_cast<const UnitDesc *>(blob + h.off_units)[it.unit], s_cm[warp], s_tb[warp]);
         const uint32_t mid = ut.mid;   // mid-line idle state (pm_library.cc)
         const unsigned long long a = it.a, b = it.a + it.len;
         const unsigned long long c = (it.len + 31) / 32;
         const unsigned long long ca = min(b, a + lane * c), cb = min(b, ca + c);
         auto walk = [&](uint32_t s, unsigned long long p0, unsigned long long p1) {
+            if (staged) return walk_staged(text, p0, p1, s, s_tb[warp], s_cm[warp], ut.stride, ut.accept, ut.dead);
             if (ut.wide) {
                 // text as aligned 32-bit words: one load per four lookups, and off the dependent chain (byte loads in the
                 // chain were 74 % of this kernel's stall samples, and k_finalize waited 12 us for it); the accepting state is
