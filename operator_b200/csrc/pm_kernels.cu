@@ -13,6 +13,7 @@
 //   k_plan / k_check / k_check_long / k_finalize   a12 + a13: line numbers, context ranges,
 //                 secondary proximity, fp64 score
 //   k_line_starts a10: materialised line table of one pod (ballot/prefix-scan scatter)
+#include <atomic>
 #include <cub/cub.cuh>
 
 #include "pm_kernels.h"
@@ -2185,6 +2186,22 @@ cudaError_t launch_scan(const uint8_t *text, unsigned long long n_tiles, const D
     }
 }
 
+// One L1/shared-memory split for k_check and k_check_long, which run side by side.  An SM cannot hold CTAs of two kernels that want different
+// splits: it drains one kind before it takes the other.  k_check wants five CTAs of 14 KiB per SM; with the driver's own choice
+// per kernel, k_check beside k_check_long (no shared memory) started half of its CTAs 11 us late (tools_warp_trace.py).  Set once
+// per device.  (k_verify with its tables in shared memory asks for the maximum instead, see launch_confirm.  The same split for
+// ALL the small kernels was measured too: 4.29 against 4.41 TB/s with five batches in flight, 0.340 against 0.332 ms alone.)
+static void tail_carveout() {
+    static std::atomic<unsigned long long> done{0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+    if (done.load(std::memory_order_relaxed) & (1ull << dev)) return;
+    static const int pct = getenv("PM_TAIL_CARVEOUT") ? atoi(getenv("PM_TAIL_CARVEOUT")) : 40;
+    cudaFuncSetAttribute(k_check, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    cudaFuncSetAttribute(k_check_long, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    done.fetch_or(1ull << dev, std::memory_order_relaxed);
+}
+
 cudaError_t launch_prefix(const uint32_t *tile_nl, unsigned long long *tile_prefix, unsigned long long n_tiles, unsigned long long *scratch, cudaStream_t s) {
     unsigned long long n_blocks = (n_tiles + kPrefBlock - 1) / kPrefBlock;
     if (n_blocks == 0) return cudaSuccess;
@@ -2204,6 +2221,7 @@ cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, 
                            unsigned long long cand_cap, unsigned long long *tasks, unsigned long long *raw, unsigned long long raw_cap, ScanCounters *ctr,
                            int num_sms, cudaStream_t s, bool tables_in_smem) {
     if (lib.fv.log2_bits == 0) return cudaSuccess;
+    tail_carveout();
     k_confirm<<<num_sms * 8, 256, 0, s>>>(text, total_bytes, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
     stage_mark("k_confirm");
     // per-warp shared-memory budget for the task's table: the largest verify table of the library, as long as
@@ -2301,12 +2319,7 @@ cudaError_t launch_resolve(const uint8_t *text, const DeviceLibrary &lib, const 
         cudaEventRecord(fork_ev, s);
         cudaStreamWaitEvent(side, fork_ev, 0);
     }
-    {   // k_check wants five CTAs of 14 KiB per SM, k_check_long (no shared memory) runs beside it: the same L1/shared split for
-        // both, or an SM has to drain the CTAs of one before it can take CTAs of the other (half of k_check's CTAs started 11 us
-        // late, tools_warp_trace.py)
-        cudaFuncSetAttribute(k_check, cudaFuncAttributePreferredSharedMemoryCarveout, 40);
-        cudaFuncSetAttribute(k_check_long, cudaFuncAttributePreferredSharedMemoryCarveout, 40);
-    }
+    tail_carveout();
     k_check_long<<<num_sms * 16, 128, 0, fork ? side : s>>>(text, lib.blob, lib.h, items, rs.long_list, rs.long_cap, rs.results, rs.ctr);
     if (fork) cudaEventRecord(join_ev, side);
     k_check<<<num_sms * 5, kCheckWarps * 32, 0, s>>>(text, lib.blob, lib.h, items, reinterpret_cast<const Group *>(rs.groups), rs.group_cap, rs.results, rs.ctr);
