@@ -2222,7 +2222,8 @@ cudaError_t launch_confirm(const uint8_t *text, unsigned long long total_bytes, 
                            int num_sms, cudaStream_t s, bool tables_in_smem) {
     if (lib.fv.log2_bits == 0) return cudaSuccess;
     tail_carveout();
-    k_confirm<<<num_sms * 8, 256, 0, s>>>(text, total_bytes, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
+    static const int confirm_ctas = getenv("PM_CONFIRM_CTAS") ? atoi(getenv("PM_CONFIRM_CTAS")) : 8;
+    k_confirm<<<num_sms * confirm_ctas, 256, 0, s>>>(text, total_bytes, lib.fv, cand, cand_cap, tasks, raw_cap, ctr);
     stage_mark("k_confirm");
     // per-warp shared-memory budget for the task's table: the largest verify table of the library, as long as
     // 12 CTAs still fit an SM (the register limit of this kernel); larger tables are walked through L1.  Only with

@@ -278,6 +278,7 @@ struct DevWork {
     DeviceLibrary dl;                     // the library view this scan runs with (copied under adapt_mu)
     cudaEvent_t fork_ev[3] = {nullptr, nullptr, nullptr}, join_ev[3] = {nullptr, nullptr, nullptr};
     uint64_t key_cap = 0;   // entries of rs_aux (keys the resolve stage can plan in one go)
+    bool post_restarted = false;
     cudaEvent_t e[10] = {nullptr};   // 0 h2d0, 1 h2d1, 2 scan0, 3 scan1, 4 mid, 5 post0, 6 post1, 7 d2h1, 8 dfa0, 9 dfa1
     uint64_t n_events = 0, n_cand = 0, n_verified = 0;
     bool locked = false, staged = false, scanned = false;
@@ -866,14 +867,16 @@ int scan_async(pm_batch *b) {
                           w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), w.sms_post, w.stream, /*tables_in_smem=*/d->depth == 1 || verify_smem_always()));
         w.launches += 1 + 2 + (np ? 1 : 0) + (dl.fv.log2_bits ? 2 : 0);
         w.mark("k_verify");
-        CU(cudaEventRecord(w.e[8], w.stream));
+        // (a timing event between two kernels keeps the second from starting until the first has drained and the stamp is
+        // written, 1-2 us each: none where there is nothing to time)
+        if (dl.h.n_groups) CU(cudaEventRecord(w.e[8], w.stream));
         for (uint32_t g = 0; g < dl.h.n_groups; g++) {
             const GroupDesc &gd = reinterpret_cast<const GroupDesc *>(b->lib->lib.blob.data() + dl.h.off_groups)[g];
             CU(launch_dfa_scan(w.text.as<uint8_t>(), w.total, dl, w.table(), (int)g, gd.wide != 0, (size_t)gd.nstates * gd.stride * 2,
                                w.raw.as<unsigned long long>(), w.raw_cap, w.ctr.as<ScanCounters>(), w.sms_post, w.stream));
             w.launches++;
         }
-        CU(cudaEventRecord(w.e[9], w.stream));
+        if (dl.h.n_groups) CU(cudaEventRecord(w.e[9], w.stream));
         // ordering and de-duplication run beside plan/check (which take the raw queue as it is);
         // k_finalize waits for them and places each row at its key's rank
         CU(cudaEventRecord(w.fork_ev[2], w.stream));
@@ -886,8 +889,7 @@ int scan_async(pm_batch *b) {
         w.launches += 5;
         CU(cudaStreamWaitEvent(w.stream, w.join_ev[0], 0));
         w.mark("join prefix/pods");
-        CU(cudaEventRecord(w.e[4], w.stream));
-        CU(cudaEventRecord(w.e[5], w.stream));
+        w.post_restarted = false;   // e[4] / e[5] bracket the host's part when the resolve stage has to be run again (finish)
         if ((rc = enqueue_resolve(b, w, true))) return rc;
         CU(cudaStreamWaitEvent(w.stream, w.pods_copied, 0));
     }
@@ -934,7 +936,9 @@ int finish(pm_batch *b, pm_result_view *out) {
         if (big) {
             const uint64_t n_raw = c->n_raw;
             int rc;
+            CU(cudaEventRecord(w.e[4], w.stream));   // (the stream is idle: the host has just read the counters)
             CU(cudaEventRecord(w.e[5], w.stream));
+            w.post_restarted = true;
             size_t tb = sort_temp_bytes(n_raw);
             if ((rc = get(d->pool, n_raw * 8, w.sorted))) return rc;
             if ((rc = get(d->pool, tb, w.temp))) return rc;
@@ -980,13 +984,17 @@ int finish(pm_batch *b, pm_result_view *out) {
         float a = 0, s = 0, p1 = 0, p2 = 0, dd = 0, tt = 0;
         cudaEventElapsedTime(&a, w.e[0], w.e[1]);
         cudaEventElapsedTime(&s, w.e[2], w.e[3]);
-        cudaEventElapsedTime(&p1, w.e[3], w.e[4]);
-        cudaEventElapsedTime(&p2, w.e[5], w.e[6]);
+        if (w.post_restarted) {
+            cudaEventElapsedTime(&p1, w.e[3], w.e[4]);
+            cudaEventElapsedTime(&p2, w.e[5], w.e[6]);
+        } else {
+            cudaEventElapsedTime(&p1, w.e[3], w.e[6]);
+        }
         cudaEventElapsedTime(&dd, w.e[6], w.e[7]);
         cudaEventElapsedTime(&tt, w.e[2], w.e[7]);
         ms_total = std::max<double>(ms_total, tt);
         float df = 0;
-        cudaEventElapsedTime(&df, w.e[8], w.e[9]);
+        if (w.dl.h.n_groups) cudaEventElapsedTime(&df, w.e[8], w.e[9]);
         if (w.dl.h.n_groups) ms_dfa = std::max<double>(ms_dfa, df);
         ms_h2d = std::max<double>(ms_h2d, a);
         ms_scan = std::max<double>(ms_scan, s);
