@@ -632,22 +632,20 @@ __device__ __forceinline__ UnitTables unit_tables(const uint8_t *blob, const Blo
 __device__ bool line_matches(const uint8_t *text, unsigned long long a, unsigned long long b, const UnitTables &t) {
     uint32_t s = 0;
     if (t.wide) {
-        // 256-column table: one dependent lookup per byte.  The text comes in aligned 16-byte pieces: the lanes of a warp
-        // walk 32 different lines, so every text load of the warp touches 32 cache lines, and with 4-byte loads those
-        // were 60 % of the L1 wavefronts this kernel is bound by (tools_warp_trace.py: 110 ns per line byte).  The
-        // accepting state is sticky and the dead state absorbing, so both are tested once per piece.
+        // 256-column table in global memory (units whose table does not fit k_check's shared-memory budget): one dependent
+        // lookup per byte, the text in aligned 16-byte pieces.  The accepting state is sticky and the dead state absorbing,
+        // so both are tested once per piece.
         const uint16_t *w = t.wide;
         for (unsigned long long p = a & ~15ull; p < b && s != t.accept && s != t.dead; p += 16) {
             const uint4 v = *reinterpret_cast<const uint4 *>(text + p);
             const uint32_t x[4] = {v.x, v.y, v.z, v.w};
-            if (p >= a && p + 16 <= b) {
+            // one code path for whole and partial pieces (see walk_staged): bytes outside the line are looked up and dropped
+            const int lo = p >= a ? 0 : (int)(a - p), hi = p + 16 <= b ? 16 : (int)(b - p);
+            const uint32_t valid = (0xFFFFu >> (16 - hi)) & (0xFFFFu << lo);
 #pragma unroll
-                for (int j = 0; j < 16; j++) s = w[(s << 8) | ((x[j >> 2] >> (8 * (j & 3))) & 0xFFu)];
-            } else {   // first / last piece of the line
-                const int lo = p >= a ? 0 : (int)(a - p), hi = p + 16 <= b ? 16 : (int)(b - p);
-#pragma unroll
-                for (int j = 0; j < 16; j++)
-                    if (j >= lo && j < hi) s = w[(s << 8) | ((x[j >> 2] >> (8 * (j & 3))) & 0xFFu)];
+            for (int j = 0; j < 16; j++) {
+                const uint32_t nx = w[(s << 8) | ((x[j >> 2] >> (8 * (j & 3))) & 0xFFu)];
+                s = ((valid >> j) & 1u) ? nx : s;
             }
         }
         if (s == t.accept) return true;

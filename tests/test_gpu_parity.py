@@ -454,3 +454,45 @@ def test_http_front_end_speaks_the_parse_contract(engine):
     finally:
         srv.shutdown()
         srv.server_close()
+
+
+@pytest.mark.gpu
+def test_context_units_inside_and_outside_the_shared_memory_budget(engine):
+    """k_check walks a run of context lines through the warp's shared-memory copy of the unit's table when
+    the table fits (1536 one-byte entries) and through the 256-column table in global memory when it does
+    not: one secondary of each kind (760 and 4680 entries), lines of every length up to the long-line
+    threshold and beyond, hits at every alignment, windows that reach over the pod's ends."""
+    import random
+    rnd = random.Random(77)
+    big = r"(?i)(alpha|bravo|charlie|delta|echo|foxtrot|golf|hotel|india|juliet)[ _-](kilo|lima|mike|november|oscar|papa|quebec|romeo)[0-9]{3}"
+    small = r"connection (refused|reset|timed out) by peer [0-9]+"
+    lib = {"patterns": [
+        {"id": "a", "name": "a", "severity": "HIGH", "primary_pattern": {"regex": r"FATAL: worker crashed", "confidence": 0.9},
+         "secondary_patterns": [{"regex": big, "weight": 0.4, "proximity_window": 9}, {"regex": small, "weight": 0.3, "proximity_window": 4}],
+         "context_extraction": {"lines_before": 3, "lines_after": 4, "include_stack_trace": True}},
+        {"id": "b", "name": "b", "severity": "LOW", "primary_pattern": {"regex": r"panic: runtime error", "confidence": 0.7},
+         "secondary_patterns": [{"regex": big, "weight": 0.5, "proximity_window": 16}]},
+    ]}
+    fill = "abcdefghijklmnopqrstuvwxyz 0123456789 _-:/"
+    def filler(n):
+        return "".join(rnd.choice(fill) for _ in range(n))
+    logs = []
+    for pod in range(3):
+        lines = []
+        for i in range(1500):
+            r = rnd.random()
+            n = rnd.choice([0, 1, 7, 15, 16, 17, 31, 60, 100, 127, 128, 129, 200, 255, 256, 257, 300, 700])
+            if r < 0.03:
+                lines.append(filler(rnd.randint(0, 20)) + "FATAL: worker crashed" + filler(rnd.randint(0, 30)))
+            elif r < 0.05:
+                lines.append(filler(rnd.randint(0, 9)) + "panic: runtime error: index out of range")
+            elif r < 0.12:
+                lines.append(filler(n) + rnd.choice(["Echo-Mike123", "juliet_ROMEO007", "alpha papa999", "golf-lima12"]) + filler(rnd.randint(0, 40)))
+            elif r < 0.18:
+                lines.append(filler(n) + "connection %s by peer %d" % (rnd.choice(["refused", "reset", "timed out", "closed"]), rnd.randint(0, 99)))
+            elif r < 0.24:
+                lines.append("\tat com.example.Worker.run(Worker.java:%d)" % rnd.randint(1, 999))
+            else:
+                lines.append(filler(n))
+        logs.append(("\n".join(lines) + "\n").encode())
+    check_parity(engine, lib, logs, expect_events=100)
