@@ -37,7 +37,14 @@ oracle/_build/liboracle_pcre2.so: oracle/scan_pcre2.c
 operator_b200/libpm_synth.so: operator_b200/csrc/synth/pm_synth.cc operator_b200/csrc/synth/pm_synth_gpu.cu operator_b200/csrc/synth/pm_synth_core.h
 	$(NVCC) $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-pthread -shared -o $@ operator_b200/csrc/synth/pm_synth.cc operator_b200/csrc/synth/pm_synth_gpu.cu -lcudart
 
+# Measurement build with warp time stamps in the post-scan kernels (tools_warp_trace.py); not part of `all`.
+trace: operator_b200/libpodmortem_scan_trace.so
+$(CSRC)/pm_kernels_trace.o: $(CSRC)/pm_kernels.cu $(HDRS)
+	$(NVCC) $(NVFLAGS) -DPM_TRACE -c $< -o $@ 2> $@.ptxas.log || (cat $@.ptxas.log; false)
+operator_b200/libpodmortem_scan_trace.so: $(HOST_OBJS) $(filter-out $(CSRC)/pm_kernels.o $(CSRC)/pm_kernels_trace.o,$(CU_OBJS)) $(CSRC)/pm_kernels_trace.o
+	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart
+
 clean:
 	rm -f $(CSRC)/*.o $(CSRC)/*.log operator_b200/*.so tests/support/*.so oracle/_build/*.so
 
-.PHONY: all clean
+.PHONY: all clean trace

@@ -3,8 +3,8 @@
 
 Needs a -DPM_TRACE build of the library (the stamps compile to nothing otherwise):
 
-    nvcc ... -DPM_TRACE -c operator_b200/csrc/pm_kernels.cu -o /tmp/pm_kernels_trace.o   # then link as the Makefile does
-    PM_SCAN_LIBRARY=operator_b200/libpodmortem_scan_trace.so python tools_warp_trace.py [--p-hit 1e-3]
+    make trace
+    PM_SCAN_LIBRARY=$PWD/operator_b200/libpodmortem_scan_trace.so python tools_warp_trace.py [--p-hit 1e-3]
 
 Prints, per kernel, the spread of the warps' start times, of their end times, and the time between
 consecutive stamps (percentiles over the warps that had work), all in microseconds from the first
